@@ -1,0 +1,442 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark of the RS GF(2^8) coding path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c3|c4]
+
+One "step" = one pass of the hot path (the GF(2^8) generator-matrix multiply) over one stripe batch
+of synthetic random fragments.  Default workload = BASELINE.json configs[1]: RS(10,14) encode of
+4,194,304,000 input bytes (10 fragments x 400 MiB) resident in HBM, per GPU (weak scaling: stripes
+shard across GPUs with no collective on the data path).  Inputs (4.2 GB) are far larger than L2
+(126 MB), so every step streams from HBM without an explicit flush.
+
+Prints ONE JSON line (rank 0).  `value` = input GB/s (1 GB = 1e9 B) over all GPUs with inputs already
+in HBM; `e2e` = the same through the host-buffer C-ABI call (rsgpu_encode_host: pinned host memory ->
+H2D -> kernel -> D2H, all inside the timed region); `roofline` = algorithmic bytes (k+p)*L per launch
+over the measured kernel time, against the measured HBM copy peak; `cpu_baseline` = the reference's own
+cpu-rs.c matrix_mul (oracle/_ref, else our C port) on this box's host cores.
+"""
+import argparse
+import ctypes
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+MIB = 1 << 20
+WORKLOADS = {
+    # name: (k, p, fragment bytes L, mode, description)
+    "c2": (10, 4, 400 * MIB, "encode", "RS(10,14) encode, 10 x 400 MiB device-resident fragments per GPU (BASELINE configs[1])"),
+    "c3": (10, 4, 400 * MIB, "decode", "RS(10,14) decode, 4 erased natives, GPU Gauss-Jordan inverse + reconstruct (BASELINE configs[2])"),
+    "c4": (16, 4, 256 * MIB, "encode", "RS(16,20) encode, 16 x 256 MiB fragments per GPU per step (BASELINE configs[3] stripe batch, sharded)"),
+    "c1": (4, 2, 16 * MIB, "encode", "RS(4,6) encode of a 64 MiB file's fragments (BASELINE configs[0])"),
+}
+FALLBACK_HBM_GBS = 6650.0   # /opt/skills/guides/B200_PROFILING.md, used only if MEASURED_PEAKS.json is absent
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--frag-mib", type=float, default=0, help="override fragment size (MiB) for quick checks")
+    ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-slots", type=int, default=0)
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own matrix_mul (oracle/_ref) or our C port of it (oracle/), all host cores
+# ------------------------------------------------------------------------------------------------
+
+def _cpu_matmul_fn():
+    """returns (kind, callable(A, B, C, n, p, m)) -- ctypes releases the GIL during the call."""
+    from oracle_lib import ORACLE_SO, REF_SO, Oracle, Reference
+    u8p = ctypes.POINTER(ctypes.c_uint8)
+    if os.path.exists(REF_SO):
+        ref = Reference()
+        return "reference", ref.L.matrix_mul, ref.gen_encoding_matrix
+    orc = Oracle()
+    return "port", orc.L.orc_matrix_mul, orc.gen_encoding_matrix
+
+
+class CpuArm:
+    """C = V * B on `threads` host threads, each on its own contiguous stripe slice (stripes are
+    independent, which is also how the GPU path shards).  Buffers are made once; run(nbytes) times one
+    pass over the first nbytes of input."""
+
+    def __init__(self, k, p, threads, max_input_bytes):
+        self.kind, self.fn, gen = _cpu_matmul_fn()
+        self.k, self.p, self.threads = k, p, threads
+        self.V = np.ascontiguousarray(gen(p, k))
+        self.m_max = max(4096, int(max_input_bytes // (k * threads)))
+        rng = np.random.default_rng(12345)
+        self.datas = [rng.integers(0, 256, k * self.m_max, dtype=np.uint8) for _ in range(threads)]
+        self.codes = [np.zeros(p * self.m_max, np.uint8) for _ in range(threads)]
+
+    def run(self, input_bytes):
+        """returns (seconds, input bytes processed)"""
+        u8p = ctypes.POINTER(ctypes.c_uint8)
+        m = min(self.m_max, max(4096, int(input_bytes // (self.k * self.threads))))
+
+        def work(t):
+            self.codes[t][: self.p * m] = 0      # matrix_mul accumulates into C (cpu-rs.c:194)
+            self.fn(self.V.ctypes.data_as(u8p), self.datas[t].ctypes.data_as(u8p), self.codes[t].ctypes.data_as(u8p),
+                    self.p, self.k, m)
+
+        ths = [threading.Thread(target=work, args=(t,)) for t in range(self.threads)]
+        t0 = time.perf_counter()
+        for th in ths:
+            th.start()
+        for th in ths:
+            th.join()
+        return time.perf_counter() - t0, self.k * m * self.threads
+
+
+def cpu_throughput(k, p, total_input_bytes, threads):
+    arm = CpuArm(k, p, threads, total_input_bytes)
+    dt, nb = arm.run(total_input_bytes)
+    return nb / dt / 1e9, arm.kind, dt, nb
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_reference_arm(args, rank):
+    """`--impl reference`: the reference's CPU implementation of the path, all host threads, rank 0 only."""
+    if rank != 0:
+        return
+    k, p, L, mode, desc = WORKLOADS[args.workload]
+    cores = host_cores()
+    arm = CpuArm(k, p, cores, 512 * MIB)
+    dt, nb = arm.run(64 * MIB)                       # calibration pass (untimed in the result)
+    rate = nb / dt
+    # bounded sample per step: the whole --steps K --warmup W run should take about two minutes at most
+    budget_s = 100.0
+    sample = int(min(512 * MIB, max(16 * MIB, rate * budget_s / max(1, args.steps + args.warmup))))
+    for _ in range(args.warmup):
+        arm.run(sample)
+    t_total, b_total, kind = 0.0, 0, arm.kind
+    for _ in range(args.steps):
+        dt, nb = arm.run(sample)
+        t_total += dt
+        b_total += nb
+    val = b_total / t_total / 1e9
+    line = {
+        "impl": "reference",
+        "metric": "RS(%d,%d) %s throughput, input bytes" % (k, k + p, mode),
+        "value": val, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * t_total / max(1, args.steps), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": desc, "k": k, "p": p, "note": "reference CPU path (cpu-rs.c matrix_mul) on host cores; "
+                   "each step is a bounded %d MiB-input sample of the workload" % (sample // MIB)},
+        "cpu_baseline": {"value": val, "unit": "GB/s", "cores": cores, "kind": kind,
+                         "sample": "%d MiB input per step, %d threads, each thread its own stripe slice" % (sample // MIB, cores)},
+        "e2e": {"value": val, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler
+# ------------------------------------------------------------------------------------------------
+
+class ClockSampler:
+    """nvidia-smi in loop mode for the whole run; stop(t0, t1) keeps the samples taken between the wall
+    times t0 (warm-up start) and t1 (end of the timed region)."""
+    Q = "timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "50"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self, t0, t1):
+        import datetime
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            out, _ = self.proc.communicate()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = []
+        for ln in out.splitlines():
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                rows.append((ts, float(f[1]), float(f[2]), float(f[3]),
+                             [nm for nm, v in zip(names, f[4:8]) if v.lower().startswith("active")]))
+            except ValueError:
+                continue
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sel = [r for r in rows if t0 - 0.03 <= r[0] <= t1 + 0.03]
+        window = "warm-up + timed region"
+        if not sel:     # region shorter than the sampling period: take the sample nearest to it
+            sel = [min(rows, key=lambda r: abs(r[0] - (t0 + t1) / 2))]
+            window = "nearest sample (timed region shorter than the 50 ms sampling period)"
+        reasons = sorted({nm for r in sel for nm in r[4]})
+        return {"sm_mhz": statistics.median(r[1] for r in sel), "sm_max_mhz": max(r[2] for r in sel), "reasons": reasons,
+                "power_w_max": max(r[3] for r in sel), "samples": len(sel), "window": window}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (the product path has no CPU fallback)")
+    rs = importlib.import_module("gpu-rscode_b200")
+    rs.lib()
+
+    torch.cuda.set_device(local_rank)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    n_gpus = world
+
+    k, p, L, mode, desc = WORKLOADS[args.workload]
+    if args.frag_mib:
+        L = int(args.frag_mib * MIB) // 256 * 256
+        desc += " [fragment size overridden to %d bytes]" % L
+    dev = torch.device("cuda", local_rank)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    ctx = rs.RSContext(k, p, device=local_rank)
+    if args.variant or args.threads:
+        ctx.set_tuning(variant=args.variant, threads=args.threads)
+
+    # synthetic random fragments, device resident
+    g = torch.Generator(device=dev).manual_seed(0xB200 + rank)
+    data = torch.randint(0, 256, (k, L), dtype=torch.uint8, device=dev, generator=g)
+    if mode == "encode":
+        rows_out = p
+        out = torch.empty((p, L), dtype=torch.uint8, device=dev)
+        src = data
+
+        def step():
+            ctx.encode(src, L, out, L, L, stream)
+        algo_bytes = (k + p) * L
+    else:
+        # decode: survivors = 4 parities + natives 4..9 in natural conf order; timed = GJ inverse + reconstruct
+        e = p
+        parity = torch.empty((p, L), dtype=torch.uint8, device=dev)
+        ctx.encode(data, L, parity, L, L, stream)
+        torch.cuda.synchronize()
+        order = list(range(k, k + e)) + list(range(e, k))
+        src = torch.cat([parity, data[e:]], dim=0).contiguous()
+        out = torch.empty((e, L), dtype=torch.uint8, device=dev)
+        rows_out = e
+
+        def step():
+            ctx.set_survivors(order)
+            ctx.decode_erased(src, L, out, L, L, stream)
+        algo_bytes = (k + e) * L
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    t_wall0 = time.time()
+    for _ in range(max(3, args.warmup)):
+        step()
+    barrier()
+
+    launches0 = ctx.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    ev0.record()
+    for i in range(args.steps):
+        if mode == "decode":
+            ctx.set_survivors(order)          # inverse + table build (blocks briefly; part of the step)
+            kev[i][0].record()
+            ctx.decode_erased(src, L, out, L, L, stream)
+            kev[i][1].record()
+        else:
+            kev[i][0].record()
+            step()
+            kev[i][1].record()
+    ev1.record()
+    barrier()
+    elapsed_ms = ev0.elapsed_time(ev1)
+    launches = ctx.launch_count() - launches0
+    kernel_ms = [a.elapsed_time(b) for a, b in kev]
+    clocks = sampler.stop(t_wall0, time.time()) if sampler else None
+
+    t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed_ms = float(t.item())
+    value = n_gpus * k * L * args.steps / (elapsed_ms / 1e3) / 1e9
+
+    # ---- correctness spot check of what was just timed (oracle on a 64 KiB window) ----
+    check = "skipped"
+    if rank == 0:
+        from oracle_lib import Oracle
+        orc = Oracle()
+        w0 = (L // 2) // 16 * 16
+        win = slice(w0, w0 + 65536)
+        if mode == "encode":
+            want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), data[:, win].cpu().numpy())
+        else:
+            want = data[:rows_out, win].cpu().numpy()
+        check = "ok" if (out[:, win].cpu().numpy() == want).all() else "MISMATCH"
+
+    # ---- end to end through the host-buffer C-ABI call ----
+    e2e = None
+    if not args.no_e2e:
+        e2e_L = L
+        try:
+            import psutil
+            avail = psutil.virtual_memory().available
+        except Exception:
+            avail = 64 << 30
+        need = (k + rows_out) * e2e_L * n_gpus
+        note = ""
+        while need > 0.5 * avail and e2e_L > 16 * MIB:
+            e2e_L //= 2
+            need = (k + rows_out) * e2e_L * n_gpus
+            note = " (fragment size halved to fit pinned host memory)"
+        h_in = torch.empty((k, e2e_L), dtype=torch.uint8).pin_memory()
+        h_out = torch.empty((rows_out, e2e_L), dtype=torch.uint8).pin_memory()
+        h_in.copy_(src[:, :e2e_L])
+        torch.cuda.synchronize()
+        if mode == "decode":
+            ctx.set_survivors(order)
+
+        def e2e_step():
+            if mode == "encode":
+                ctx.encode_host(h_in.data_ptr(), e2e_L, h_out.data_ptr(), e2e_L, e2e_L, args.e2e_slots)
+            else:
+                ctx.set_survivors(order)
+                ctx.decode_erased_host(h_in.data_ptr(), e2e_L, h_out.data_ptr(), e2e_L, e2e_L, args.e2e_slots)
+        e2e_steps = max(1, min(args.steps, 10))
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()          # blocks until the parity bytes are in host memory
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        e2e = {"value": n_gpus * k * e2e_L * e2e_steps / dt / 1e9, "unit": "GB/s",
+               "h2d_bytes_per_step": k * e2e_L, "d2h_bytes_per_step": rows_out * e2e_L,
+               "steps": e2e_steps, "fragment_bytes": e2e_L,
+               "api": "%s (pinned host buffers, H2D+kernel+D2H pipelined inside the call)%s" % ("rsgpu_encode_host" if mode == "encode" else "rsgpu_set_survivors + rsgpu_decode_erased_host", note)}
+        if rank == 0 and mode == "encode":
+            from oracle_lib import Oracle
+            orc = Oracle()
+            want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), h_in[:, :65536].numpy())
+            if not (h_out[:, :65536].numpy() == want).all():
+                check = "MISMATCH(e2e)"
+        del h_in, h_out
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel ----
+    peak, peak_src = FALLBACK_HBM_GBS, "fallback"
+    try:
+        mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        peak, peak_src = float(mp["hbm_gbs"]), "measured"
+    except Exception:
+        pass
+    k_ms = statistics.mean(kernel_ms)
+    achieved = algo_bytes / (k_ms / 1e3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "kernel": "k_gf_matmul", "kernel_ms_mean": k_ms,
+                "kernel_ms_min": min(kernel_ms), "algorithmic_bytes_per_launch": algo_bytes,
+                "input_gbs_kernel_only": k * L / (k_ms / 1e3) / 1e9}
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        try:
+            tr = json.load(open(prof)).get(args.workload)
+            if tr:
+                roofline["traffic"] = tr["dram_bytes_per_launch"]
+                roofline["traffic_source"] = tr.get("source")
+        except Exception:
+            pass
+
+    cpu = None
+    if n_gpus == 1 and not args.no_cpu:
+        cores = host_cores()
+        v1, kind, dt1, nb1 = cpu_throughput(k, p, 128 * MIB, 1)
+        vN, kind, dtN, nbN = cpu_throughput(k, p, 2048 * MIB if cores >= 16 else 128 * MIB * cores, cores)
+        cpu = {"value": vN, "unit": "GB/s", "cores": cores, "kind": kind,
+               "sample": "%d MiB of input (same k,p; encode matrix), %d threads each on its own stripe slice, %.1f s" % (nbN // MIB, cores, dtN),
+               "value_1core": v1, "sample_1core": "%d MiB input, %.1f s" % (nb1 // MIB, dt1)}
+
+    line = {
+        "metric": "RS(%d,%d) %s throughput, input bytes" % (k, k + p, mode),
+        "value": value, "unit": "GB/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": max(3, args.warmup),
+        "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": desc, "k": k, "p": p, "fragment_bytes": L, "input_bytes_per_gpu_per_step": k * L,
+                   "l2_policy": "inputs (%.1f GB) larger than L2, no flush" % (k * L / 1e9),
+                   "parallelism": "stripes sharded across %d GPU(s), no collective on the data path" % n_gpus,
+                   "variant": args.variant, "check_vs_oracle": check},
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "e2e": e2e,
+        "gpu_launches": launches * n_gpus,
+        "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

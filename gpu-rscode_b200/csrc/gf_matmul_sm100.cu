@@ -1,0 +1,324 @@
+// gf_matmul_sm100.cu -- THE hot path: C (rows x len) = M (rows x k) * B (k x len) over GF(2^8).
+//
+// Replaces the reference's matrix_mul<long long> / matrix_mul<unsigned char> kernels and their
+// launchers encode_chunk / decode_chunk (src/matrix.cu:232-323, 335-407, 767-905).
+//
+// Design (sm_100a, HBM-bound integer/byte work -- no tensor cores):
+//   * every thread owns 16-byte columns: one 128-bit coalesced load per input fragment, one
+//     128-bit store per output row, grid-stride over the stripe (persistent grid sized from the
+//     SM count); input bytes are read from HBM exactly once, outputs written exactly once.
+//   * GF multiply = per-coefficient split-nibble product tables in shared memory.  For input
+//     fragment j there are two 16-entry tables (low nibble, high nibble); an entry packs the
+//     products for ALL output rows of the group, one byte per row (4 rows -> one 32-bit word,
+//     8 rows -> 64 bit), so ONE conflict-free shared-memory lookup per nibble yields the
+//     contribution to every parity at once: 2 lookups per input byte regardless of the row count.
+//     A 16-entry table of 4-byte words spans 16 distinct banks, and equal indices broadcast, so a
+//     warp's 32 random nibbles never conflict.
+//   * multiply-accumulate is XOR into one accumulator word per byte position (bytes = rows); a
+//     4x4 byte transpose with PRMT at the end turns them into the row-major 16-byte stores.
+//   * the next batch of fragment loads is issued before the current batch is consumed (register
+//     double buffering), so each thread always has JB*16 bytes in flight.
+//   The reference instead does, per byte-product, two log lookups, an add and an exp lookup in
+//   bank-conflicted shared tables, re-stages A and B into shared memory redundantly in every
+//   thread with two __syncthreads per tile, and moves 8 bytes per access.
+#include "rs_internal.h"
+
+namespace rsgpu {
+namespace {
+
+__device__ __forceinline__ uint4 ldg_stream(const uint8_t *p)
+{
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ void stg_stream(uint8_t *p, uint4 v)
+{
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+__device__ __forceinline__ uint32_t lds32(uint32_t addr)
+{
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+__device__ __forceinline__ uint2 lds64(uint32_t addr)
+{
+    uint2 v;
+    asm("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
+
+// Accumulators for one 16-byte column: W=4 -> 16 words (byte r of word b = row r at byte position b),
+// W=8 -> 16 x 2 words.
+template <int W> struct Acc;
+template <> struct Acc<4> { uint32_t a[16]; };
+template <> struct Acc<8> { uint32_t a[16]; uint32_t b[16]; };
+
+template <int W> __device__ __forceinline__ void acc_clear(Acc<W> &acc);
+template <> __device__ __forceinline__ void acc_clear<4>(Acc<4> &acc)
+{
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc.a[i] = 0;
+}
+template <> __device__ __forceinline__ void acc_clear<8>(Acc<8> &acc)
+{
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { acc.a[i] = 0; acc.b[i] = 0; }
+}
+
+// Scaled table offsets (index * W) of the 8 nibbles of one 32-bit data word.
+// EX = 0: shift + mask per nibble.  EX = 1: two masks per word, PRMT byte extract per nibble.
+// EX = 2: two masks per word, DP4A byte extract that also adds the table base.
+template <int W, int EX>
+__device__ __forceinline__ void mac_word(uint32_t w, uint32_t tlo, uint32_t thi, Acc<W> &acc, int pos0)
+{
+    constexpr int SH = (W == 4) ? 2 : 3;            // log2(W)
+    constexpr uint32_t M1 = 0xFu << SH;             // one scaled nibble
+    constexpr uint32_t M4 = M1 * 0x01010101u;       // four of them
+    uint32_t olo[4], ohi[4];
+    if constexpr (EX == 0) {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            // low nibble of byte b sits at bit 8b, wanted at bit SH: shift right by 8b-SH (left for b = 0)
+            const uint32_t lo = (b == 0) ? (w << SH) : (w >> (8 * b - SH));
+            olo[b] = tlo + (lo & M1);
+            ohi[b] = thi + ((w >> (8 * b + 4 - SH)) & M1);
+        }
+    } else {
+        const uint32_t wl = (w << SH) & M4;
+        const uint32_t wh = (w >> (4 - SH)) & M4;
+        if constexpr (EX == 1) {
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                olo[b] = tlo + __byte_perm(wl, 0u, 0x4440u + b);
+                ohi[b] = thi + __byte_perm(wh, 0u, 0x4440u + b);
+            }
+        } else {
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                olo[b] = __dp4a(wl, 1u << (8 * b), tlo);
+                ohi[b] = __dp4a(wh, 1u << (8 * b), thi);
+            }
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        if constexpr (W == 4) {
+            acc.a[pos0 + b] ^= lds32(olo[b]) ^ lds32(ohi[b]);
+        } else {
+            const uint2 l = lds64(olo[b]), h = lds64(ohi[b]);
+            acc.a[pos0 + b] ^= l.x ^ h.x;
+            acc.b[pos0 + b] ^= l.y ^ h.y;
+        }
+    }
+}
+
+template <int W, int EX>
+__device__ __forceinline__ void mac_vec(const uint4 &d, uint32_t tj, Acc<W> &acc)
+{
+    const uint32_t tlo = tj, thi = tj + 16 * W;
+    mac_word<W, EX>(d.x, tlo, thi, acc, 0);
+    mac_word<W, EX>(d.y, tlo, thi, acc, 4);
+    mac_word<W, EX>(d.z, tlo, thi, acc, 8);
+    mac_word<W, EX>(d.w, tlo, thi, acc, 12);
+}
+
+// 16 accumulator words (byte r = row r) -> 4 row vectors of 16 bytes.
+__device__ __forceinline__ void transpose_store(const uint32_t *a, uint8_t *out, size_t out_pitch, size_t off,
+                                                int row0, int nrows)
+{
+    uint32_t r[4][4];   // r[row][q]
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint32_t a0 = a[4 * q], a1 = a[4 * q + 1], a2 = a[4 * q + 2], a3 = a[4 * q + 3];
+        const uint32_t t0 = __byte_perm(a0, a1, 0x5140), t1 = __byte_perm(a2, a3, 0x5140);
+        const uint32_t t2 = __byte_perm(a0, a1, 0x7362), t3 = __byte_perm(a2, a3, 0x7362);
+        r[0][q] = __byte_perm(t0, t1, 0x5410);
+        r[1][q] = __byte_perm(t0, t1, 0x7632);
+        r[2][q] = __byte_perm(t2, t3, 0x5410);
+        r[3][q] = __byte_perm(t2, t3, 0x7632);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        if (i < nrows)
+            stg_stream(out + (size_t)(row0 + i) * out_pitch + off, make_uint4(r[i][0], r[i][1], r[i][2], r[i][3]));
+}
+
+template <int JB>
+__device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *in, size_t in_pitch, size_t off,
+                                           int j0, int k)
+{
+#pragma unroll
+    for (int jj = 0; jj < JB; ++jj) {
+        int j = j0 + jj;
+        j = j < k ? j : k - 1;     // padded fragments re-read a valid row; their tables are all zero
+        d[jj] = ldg_stream(in + (size_t)j * in_pitch + off);
+    }
+}
+
+// W: table entry bytes (4: up to 4 output rows, 8: up to 8).  JB: fragments per load batch.
+// kb = number of batches (kb*JB >= k, kb*JB <= kpad).
+template <int W, int JB, int EX>
+__global__ void __launch_bounds__(256)
+k_gf_matmul(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
+            const uint32_t *__restrict__ tab, int tab_vec4, int k, int kb, int nrows, size_t nvec)
+{
+    extern __shared__ __align__(16) uint32_t s_tab[];
+    for (int i = threadIdx.x; i < tab_vec4; i += blockDim.x)
+        reinterpret_cast<uint4 *>(s_tab)[i] = reinterpret_cast<const uint4 *>(tab)[i];
+    __syncthreads();
+    const uint32_t tb = (uint32_t)__cvta_generic_to_shared(s_tab);
+
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint4 nxt[JB];
+    if (v < nvec) load_batch<JB>(nxt, in, in_pitch, v * 16, 0, k);
+
+    while (v < nvec) {
+        Acc<W> acc;
+        acc_clear<W>(acc);
+        const size_t vn = v + stride;
+        for (int b = 0; b < kb; ++b) {
+            uint4 cur[JB];
+#pragma unroll
+            for (int jj = 0; jj < JB; ++jj) cur[jj] = nxt[jj];
+            if (b + 1 < kb)
+                load_batch<JB>(nxt, in, in_pitch, v * 16, (b + 1) * JB, k);
+            else if (vn < nvec)
+                load_batch<JB>(nxt, in, in_pitch, vn * 16, 0, k);
+            const uint32_t t0 = tb + (uint32_t)(b * JB) * (32 * W);
+#pragma unroll
+            for (int jj = 0; jj < JB; ++jj) mac_vec<W, EX>(cur[jj], t0 + jj * (32 * W), acc);
+        }
+        transpose_store(acc.a, out, out_pitch, v * 16, 0, nrows);
+        if constexpr (W == 8) transpose_store(acc.b, out, out_pitch, v * 16, 4, nrows - 4);
+        v = vn;
+    }
+}
+
+// Byte-granular fallback: heads/tails shorter than 16 bytes and buffers that are not 16-byte aligned
+// (the reference's matrix_mul<unsigned char>, src/matrix.cu:335-407, used whenever size % 8 != 0).
+template <int W>
+__global__ void __launch_bounds__(256)
+k_gf_matmul_bytes(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
+                  const uint32_t *__restrict__ tab, int k, int nrows, size_t c0, size_t len)
+{
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; c < len; c += stride) {
+        uint32_t a = 0, b = 0;
+        for (int j = 0; j < k; ++j) {
+            const unsigned x = in[(size_t)j * in_pitch + c];
+            const uint32_t *tl = tab + (size_t)j * 32 * (W / 4);
+            const uint32_t *th = tl + 16 * (W / 4);
+            if (W == 4) {
+                a ^= __ldg(tl + (x & 15u)) ^ __ldg(th + (x >> 4));
+            } else {
+                a ^= __ldg(tl + 2 * (x & 15u)) ^ __ldg(th + 2 * (x >> 4));
+                b ^= __ldg(tl + 2 * (x & 15u) + 1) ^ __ldg(th + 2 * (x >> 4) + 1);
+            }
+        }
+        for (int r = 0; r < nrows; ++r) {
+            const uint32_t wv = r < 4 ? a : b;
+            out[(size_t)r * out_pitch + c] = (uint8_t)(wv >> (8 * (r & 3)));
+        }
+    }
+}
+
+using MatmulFn = void (*)(const uint8_t *, size_t, uint8_t *, size_t, const uint32_t *, int, int, int, int, size_t);
+
+template <int W, int EX>
+MatmulFn pick_jb(int jb)
+{
+    switch (jb) {
+    case 1: return k_gf_matmul<W, 1, EX>;
+    case 2: return k_gf_matmul<W, 2, EX>;
+    case 3: return k_gf_matmul<W, 3, EX>;
+    case 4: return k_gf_matmul<W, 4, EX>;
+    case 5: return k_gf_matmul<W, 5, EX>;
+    case 6: return k_gf_matmul<W, 6, EX>;
+    case 7: return k_gf_matmul<W, 7, EX>;
+    default: return k_gf_matmul<W, 8, EX>;
+    }
+}
+
+MatmulFn pick_kernel(int width, int jb, int ex)
+{
+    if (width == 4) {
+        if (ex == 1) return pick_jb<4, 1>(jb);
+        if (ex == 2) return pick_jb<4, 2>(jb);
+        return pick_jb<4, 0>(jb);
+    }
+    if (ex == 1) return pick_jb<8, 1>(jb);
+    if (ex == 2) return pick_jb<8, 2>(jb);
+    return pick_jb<8, 0>(jb);
+}
+
+// Fragments per load batch: the largest divisor of k in 4..8 (no padded fragments), else 8 (or k).
+int choose_jb(int k)
+{
+    if (k <= 8) return k;
+    for (int jb = 8; jb >= 4; --jb)
+        if (k % jb == 0) return jb;
+    return 8;
+}
+
+}  // namespace
+
+cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
+                                const uint8_t *in, size_t in_pitch, uint8_t *out, size_t out_pitch,
+                                size_t len, const Tuning &tune, const DeviceInfo &dev,
+                                cudaStream_t s, long long *launches)
+{
+    if (len == 0) return cudaSuccess;
+    uint8_t *out_g = out + (size_t)g.row0 * out_pitch;
+    const bool aligned = (((uintptr_t)in | (uintptr_t)out_g | in_pitch | out_pitch) & 15u) == 0;
+    const size_t nvec = aligned ? len / 16 : 0;
+    const int threads = tune.threads > 0 ? tune.threads : 256;
+
+    if (nvec) {
+        const int jb = choose_jb(k);
+        const int kb = (k + jb - 1) / jb;           // kb*jb <= kpad because kpad is k rounded up to 8
+        const int ex = tune.variant % 10;
+        MatmulFn fn = pick_kernel(g.width, jb, ex);
+        const size_t smem = (size_t)kpad * 32 * g.width;
+        if (smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+        }
+        int occ = 0;
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)fn, threads, smem);
+        if (e != cudaSuccess) return e;
+        if (occ < 1) occ = 1;
+        size_t want = (nvec + threads - 1) / threads;
+        size_t cap = (size_t)dev.sm_count * occ;
+        if (tune.max_blocks > 0 && (size_t)tune.max_blocks < cap) cap = tune.max_blocks;
+        const unsigned grid = (unsigned)(want < cap ? want : cap);
+        fn<<<grid, threads, smem, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, (int)(smem / 16), k, kb, g.nrows, nvec);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        if (launches) ++*launches;
+    }
+    const size_t c0 = nvec * 16;
+    if (c0 < len) {
+        const size_t rem = len - c0;
+        size_t blocks = (rem + 255) / 256;
+        const size_t cap = (size_t)dev.sm_count * 8;
+        if (blocks > cap) blocks = cap;
+        if (g.width == 4)
+            k_gf_matmul_bytes<4><<<(unsigned)blocks, 256, 0, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, k, g.nrows, c0, len);
+        else
+            k_gf_matmul_bytes<8><<<(unsigned)blocks, 256, 0, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, k, g.nrows, c0, len);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        if (launches) ++*launches;
+    }
+    return cudaSuccess;
+}
+
+}  // namespace rsgpu

@@ -1,0 +1,48 @@
+// rs_ctx.h -- the context object behind the opaque rsgpu_ctx handle (internal).
+#pragma once
+#include "rs_internal.h"
+
+constexpr int kMaxSlots = 16;
+
+struct rsgpu_ctx {
+    int device = 0;
+    int k = 0, p = 0;
+    rsgpu::DeviceInfo dev;
+    rsgpu::GfTables gf;
+    rsgpu::Tuning tune;
+    cudaStream_t setup_stream = nullptr;
+
+    uint8_t *d_total = nullptr;   // (k+p) x k : [I ; V] (or caller supplied)
+    uint8_t *d_sub = nullptr;     // k x k     : survivor rows, input of the inversion
+    int *d_rows = nullptr;        // row-index list for the gather kernel
+    int *d_flag = nullptr;        // singular flag written by the inversion kernel
+
+    rsgpu::Plan enc;              // p x k generator
+    rsgpu::Plan dec_full;         // k x k inverse (reference-semantic decode)
+    rsgpu::Plan dec_erased;       // e x k rows of the inverse for the erased natives
+    rsgpu::Plan scratch;          // rsgpu_matmul's caller-supplied matrix
+
+    bool have_survivors = false;
+    int survivors[256];
+    int erased[256];
+    int n_erased = 0;
+
+    long long launches = 0;
+
+    // host-memory pipeline (pipeline.cu): per-slot stream and device staging buffers
+    int n_slots = 0;
+    cudaStream_t slot_stream[kMaxSlots] = {};
+    uint8_t *slot_in[kMaxSlots] = {};
+    uint8_t *slot_out[kMaxSlots] = {};
+    size_t slot_pitch = 0;        // bytes per fragment row in a slot buffer
+    int slot_in_rows = 0, slot_out_rows = 0;
+};
+
+namespace rsgpu {
+int fail_cuda(cudaError_t e, const char *what);
+int fail_msg(int code, const char *msg);
+int ctx_bind(const rsgpu_ctx *c);
+int plan_apply(rsgpu_ctx *c, const Plan &pl, const uint8_t *in, size_t in_pitch, uint8_t *out, size_t out_pitch,
+               size_t len, cudaStream_t s);
+void pipeline_free(rsgpu_ctx *c);
+}  // namespace rsgpu

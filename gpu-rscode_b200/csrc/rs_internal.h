@@ -1,0 +1,76 @@
+// rs_internal.h -- declarations shared by the .cu files of librsgpu.so (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace rsgpu {
+
+// GF(2^8), primitive polynomial 0x11D (octal 0435: reference src/matrix.cu:49, src/cpu-rs.c:37).
+constexpr unsigned kPoly = 0x11D;
+constexpr int kExpSize = 512;   // exp[0..509] doubled so exp[log a + log b] needs no modulo; 510,511 = 0
+constexpr int kLogSize = 256;
+
+// Device-resident field tables: d_exp[kExpSize] then d_log[kLogSize], contiguous.
+struct GfTables {
+    uint8_t *d_exp = nullptr;
+    uint8_t *d_log = nullptr;
+};
+
+// One group of output rows that a single multiply launch produces.  The product table holds, per
+// input fragment j and nibble position (lo, hi), 16 entries of W bytes: entry n = the products of n
+// (or n<<4) with the coefficients of up to W rows, one byte per row.
+struct RowGroup {
+    int row0 = 0;       // first output row of this group
+    int nrows = 0;      // 1..8
+    int width = 4;      // bytes per table entry: 4 (<= 4 rows) or 8 (<= 8 rows)
+    uint32_t *d_tab = nullptr;   // points into Plan::d_tabs
+    size_t tab_words = 0;        // kpad * 2 * 16 * width / 4
+};
+
+constexpr int kMaxGroups = 32;   // 255 rows / 8
+
+// A coding matrix (rows x k) ready to be applied: device copy of the matrix + product tables.
+struct Plan {
+    int rows = 0;
+    int k = 0;
+    int kpad = 0;                 // k rounded up to a multiple of 8 (zero tables behind k)
+    int ngroups = 0;
+    RowGroup grp[kMaxGroups];
+    uint8_t *d_matrix = nullptr;  // rows x k
+    uint32_t *d_tabs = nullptr;   // all groups back to back
+    size_t tabs_bytes = 0;
+    bool valid = false;
+};
+
+struct Tuning {
+    int variant = 0;      // 0 = default (see gf_matmul_sm100.cu)
+    int threads = 0;      // 0 = default
+    int max_blocks = 0;   // 0 = persistent grid from SM count
+};
+
+// ---- gf_tables.cu ---------------------------------------------------------------------------
+cudaError_t launch_build_gf_tables(uint8_t *d_exp, uint8_t *d_log, cudaStream_t s);
+cudaError_t launch_gen_total_matrix(uint8_t *d_total, int k, int p, const GfTables &gf, cudaStream_t s);
+cudaError_t launch_gather_rows(const uint8_t *d_total, int k, const int *d_rows, int nrows,
+                               uint8_t *d_out, cudaStream_t s);
+cudaError_t launch_build_product_tables(const uint8_t *d_matrix, int k, int kpad, int row0, int nrows,
+                                        int width, uint32_t *d_tab, const GfTables &gf, cudaStream_t s);
+
+// ---- gj_inverse.cu --------------------------------------------------------------------------
+// d_flag[0] = 0 ok, 1 singular.  d_in is not modified.  One block does the whole inversion.
+cudaError_t launch_gj_invert(const uint8_t *d_in, uint8_t *d_inv, int n, int *d_flag,
+                             const GfTables &gf, cudaStream_t s);
+
+// ---- gf_matmul_sm100.cu ---------------------------------------------------------------------
+struct DeviceInfo {
+    int sm_count = 0;
+    int max_smem_optin = 0;
+};
+// out rows [g.row0, g.row0+g.nrows) = matrix rows * in, bytes [0, len).  *launches += kernels launched.
+cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
+                                const uint8_t *in, size_t in_pitch, uint8_t *out, size_t out_pitch,
+                                size_t len, const Tuning &tune, const DeviceInfo &dev,
+                                cudaStream_t s, long long *launches);
+
+}  // namespace rsgpu

@@ -1,0 +1,453 @@
+// rsgpu_abi.cu -- the extern "C" boundary of librsgpu.so (declared in include/rsgpu.h).
+//
+// Context management, plan (product table) construction and the device-pointer entry points.
+// The host-memory pipeline lives in pipeline.cu.  No torch, no CPU fallback: if CUDA is not usable
+// every entry point fails with RSGPU_ECUDA.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+
+#include "../../include/rsgpu.h"
+#include "rs_ctx.h"
+
+using namespace rsgpu;
+
+namespace rsgpu {
+
+static thread_local char g_err[512] = "";
+
+int fail_cuda(cudaError_t e, const char *what)
+{
+    snprintf(g_err, sizeof g_err, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+    return RSGPU_ECUDA;
+}
+
+int fail_msg(int code, const char *msg)
+{
+    snprintf(g_err, sizeof g_err, "%s", msg);
+    return code;
+}
+
+#define CK(call)                                                   \
+    do {                                                           \
+        cudaError_t e__ = (call);                                  \
+        if (e__ != cudaSuccess) return fail_cuda(e__, #call);      \
+    } while (0)
+
+void plan_free(Plan &pl)
+{
+    if (pl.d_matrix) cudaFree(pl.d_matrix);
+    if (pl.d_tabs) cudaFree(pl.d_tabs);
+    pl = Plan();
+}
+
+// Allocate a plan for `rows` x k; rows are cut into groups of 8 (64-bit table entries) with a last
+// group of <= 4 rows using 32-bit entries.
+int plan_alloc(Plan &pl, int rows, int k)
+{
+    plan_free(pl);
+    pl.rows = rows;
+    pl.k = k;
+    pl.kpad = (k + 7) / 8 * 8;
+    pl.ngroups = 0;
+    size_t words = 0;
+    for (int r0 = 0; r0 < rows;) {
+        RowGroup &g = pl.grp[pl.ngroups++];
+        const int left = rows - r0;
+        g.row0 = r0;
+        g.nrows = left > 8 ? 8 : left;
+        g.width = g.nrows > 4 ? 8 : 4;
+        g.tab_words = (size_t)pl.kpad * 32 * g.width / 4;
+        words += g.tab_words;
+        r0 += g.nrows;
+    }
+    pl.tabs_bytes = words * 4;
+    CK(cudaMalloc(&pl.d_matrix, (size_t)rows * k));
+    CK(cudaMalloc(&pl.d_tabs, pl.tabs_bytes));
+    size_t off = 0;
+    for (int g = 0; g < pl.ngroups; ++g) {
+        pl.grp[g].d_tab = pl.d_tabs + off;
+        off += pl.grp[g].tab_words;
+    }
+    return RSGPU_OK;
+}
+
+// d_matrix must already hold the rows x k matrix (device); builds every group's tables on `s`.
+int plan_build_tables(rsgpu_ctx *c, Plan &pl, cudaStream_t s)
+{
+    for (int g = 0; g < pl.ngroups; ++g) {
+        const RowGroup &rg = pl.grp[g];
+        CK(launch_build_product_tables(pl.d_matrix, pl.k, pl.kpad, rg.row0, rg.nrows, rg.width, rg.d_tab, c->gf, s));
+        ++c->launches;
+    }
+    pl.valid = true;
+    return RSGPU_OK;
+}
+
+int plan_apply(rsgpu_ctx *c, const Plan &pl, const uint8_t *in, size_t in_pitch, uint8_t *out, size_t out_pitch,
+               size_t len, cudaStream_t s)
+{
+    if (!pl.valid) return fail_msg(RSGPU_ESTATE, "coding plan not built");
+    for (int g = 0; g < pl.ngroups; ++g)
+        CK(launch_matmul_group(pl.grp[g], pl.k, pl.kpad, in, in_pitch, out, out_pitch, len, c->tune, c->dev, s,
+                               &c->launches));
+    return RSGPU_OK;
+}
+
+int ctx_bind(const rsgpu_ctx *c)
+{
+    CK(cudaSetDevice(c->device));
+    return RSGPU_OK;
+}
+
+static int ctx_create(rsgpu_ctx **out, int device, int k, int p, const uint8_t *total)
+{
+    if (!out) return fail_msg(RSGPU_EINVAL, "out is NULL");
+    *out = nullptr;
+    if (k < 1 || k > RSGPU_MAX_K || p < 0 || p > 255) return fail_msg(RSGPU_EINVAL, "need 1 <= k <= 255, 0 <= p <= 255");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail_msg(RSGPU_EINVAL, "no such CUDA device");
+    CK(cudaSetDevice(device));
+
+    rsgpu_ctx *c = new (std::nothrow) rsgpu_ctx();
+    if (!c) return fail_msg(RSGPU_ENOMEM, "host allocation failed");
+    c->device = device;
+    c->k = k;
+    c->p = p;
+    int rc = RSGPU_OK;
+    auto bail = [&](int code) { rsgpu_destroy(c); return code; };
+
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return bail(fail_msg(RSGPU_ECUDA, "cudaGetDeviceProperties failed"));
+    c->dev.sm_count = prop.multiProcessorCount;
+    c->dev.max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+
+    cudaError_t e;
+    if ((e = cudaStreamCreateWithFlags(&c->setup_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(fail_cuda(e, "cudaStreamCreate"));
+    uint8_t *d_gf = nullptr;
+    if ((e = cudaMalloc(&d_gf, kExpSize + kLogSize)) != cudaSuccess) return bail(fail_cuda(e, "cudaMalloc gf tables"));
+    c->gf.d_exp = d_gf;
+    c->gf.d_log = d_gf + kExpSize;
+    if ((e = cudaMalloc(&c->d_total, (size_t)(k + p) * k)) != cudaSuccess) return bail(fail_cuda(e, "cudaMalloc total matrix"));
+    if ((e = cudaMalloc(&c->d_sub, (size_t)k * k)) != cudaSuccess) return bail(fail_cuda(e, "cudaMalloc sub matrix"));
+    if ((e = cudaMalloc(&c->d_rows, sizeof(int) * 256)) != cudaSuccess) return bail(fail_cuda(e, "cudaMalloc row list"));
+    if ((e = cudaMalloc(&c->d_flag, sizeof(int))) != cudaSuccess) return bail(fail_cuda(e, "cudaMalloc flag"));
+
+    cudaStream_t s = c->setup_stream;
+    if ((e = launch_build_gf_tables(c->gf.d_exp, c->gf.d_log, s)) != cudaSuccess) return bail(fail_cuda(e, "build_gf_tables"));
+    ++c->launches;
+    if (total) {
+        if ((e = cudaMemcpyAsync(c->d_total, total, (size_t)(k + p) * k, cudaMemcpyHostToDevice, s)) != cudaSuccess)
+            return bail(fail_cuda(e, "copy total matrix"));
+    } else {
+        if ((e = launch_gen_total_matrix(c->d_total, k, p, c->gf, s)) != cudaSuccess) return bail(fail_cuda(e, "gen_total_matrix"));
+        ++c->launches;
+    }
+    if (p > 0) {
+        if ((rc = plan_alloc(c->enc, p, k)) != RSGPU_OK) return bail(rc);
+        if ((e = cudaMemcpyAsync(c->enc.d_matrix, c->d_total + (size_t)k * k, (size_t)p * k, cudaMemcpyDeviceToDevice, s)) != cudaSuccess)
+            return bail(fail_cuda(e, "copy generator"));
+        if ((rc = plan_build_tables(c, c->enc, s)) != RSGPU_OK) return bail(rc);
+    }
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return bail(fail_cuda(e, "context set-up"));
+    *out = c;
+    return RSGPU_OK;
+}
+
+}  // namespace rsgpu
+
+extern "C" {
+
+const char *rsgpu_strerror(int code)
+{
+    switch (code) {
+    case RSGPU_OK: return "ok";
+    case RSGPU_EINVAL: return "invalid argument";
+    case RSGPU_ECUDA: return "CUDA error";
+    case RSGPU_ESINGULAR: return "survivor matrix is singular";
+    case RSGPU_ENOMEM: return "out of memory";
+    case RSGPU_ESTATE: return "call sequence error";
+    case RSGPU_ETOOBIG: return "capacity exceeded";
+    default: return "unknown error";
+    }
+}
+
+const char *rsgpu_last_error(void) { return g_err; }
+
+int rsgpu_device_count(int *count)
+{
+    if (!count) return fail_msg(RSGPU_EINVAL, "count is NULL");
+    *count = 0;
+    CK(cudaGetDeviceCount(count));
+    return RSGPU_OK;
+}
+
+int rsgpu_create(rsgpu_ctx **out, int device, int k, int p) { return ctx_create(out, device, k, p, nullptr); }
+
+int rsgpu_create_with_matrix(rsgpu_ctx **out, int device, int k, int p, const uint8_t *total_matrix)
+{
+    if (!total_matrix) return fail_msg(RSGPU_EINVAL, "total_matrix is NULL");
+    return ctx_create(out, device, k, p, total_matrix);
+}
+
+void rsgpu_destroy(rsgpu_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    pipeline_free(c);
+    plan_free(c->enc);
+    plan_free(c->dec_full);
+    plan_free(c->dec_erased);
+    plan_free(c->scratch);
+    if (c->gf.d_exp) cudaFree(c->gf.d_exp);
+    if (c->d_total) cudaFree(c->d_total);
+    if (c->d_sub) cudaFree(c->d_sub);
+    if (c->d_rows) cudaFree(c->d_rows);
+    if (c->d_flag) cudaFree(c->d_flag);
+    if (c->setup_stream) cudaStreamDestroy(c->setup_stream);
+    delete c;
+}
+
+int rsgpu_k(const rsgpu_ctx *c) { return c ? c->k : RSGPU_EINVAL; }
+int rsgpu_p(const rsgpu_ctx *c) { return c ? c->p : RSGPU_EINVAL; }
+int rsgpu_device(const rsgpu_ctx *c) { return c ? c->device : RSGPU_EINVAL; }
+long long rsgpu_launch_count(const rsgpu_ctx *c) { return c ? c->launches : 0; }
+
+int rsgpu_get_total_matrix(rsgpu_ctx *c, uint8_t *total)
+{
+    if (!c || !total) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    CK(cudaMemcpy(total, c->d_total, (size_t)(c->k + c->p) * c->k, cudaMemcpyDeviceToHost));
+    return RSGPU_OK;
+}
+
+int rsgpu_encode(rsgpu_ctx *c, const uint8_t *data_d, size_t data_pitch, uint8_t *parity_d, size_t parity_pitch,
+                 size_t len, void *stream)
+{
+    if (!c || !data_d || !parity_d) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (c->p == 0) return RSGPU_OK;
+    if ((c->k > 1 && data_pitch < len) || (c->p > 1 && parity_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    return plan_apply(c, c->enc, data_d, data_pitch, parity_d, parity_pitch, len, (cudaStream_t)stream);
+}
+
+int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
+{
+    if (!c || !idx) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    const int k = c->k, n = c->k + c->p;
+    bool have[256] = {false};
+    for (int i = 0; i < k; ++i) {
+        if (idx[i] < 0 || idx[i] >= n) return fail_msg(RSGPU_EINVAL, "fragment index out of range");
+        if (idx[i] < k) have[idx[i]] = true;
+    }
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    c->dec_full.valid = false;
+    c->dec_erased.valid = false;
+    c->n_erased = 0;
+    for (int j = 0; j < k; ++j)
+        if (!have[j]) c->erased[c->n_erased++] = j;
+    memcpy(c->survivors, idx, sizeof(int) * k);
+
+    cudaStream_t s = c->setup_stream;
+    if (!c->dec_full.d_matrix && (rc = plan_alloc(c->dec_full, k, k)) != RSGPU_OK) return rc;
+    CK(cudaMemcpyAsync(c->d_rows, idx, sizeof(int) * k, cudaMemcpyHostToDevice, s));
+    CK(launch_gather_rows(c->d_total, k, c->d_rows, k, c->d_sub, s));
+    CK(launch_gj_invert(c->d_sub, c->dec_full.d_matrix, k, c->d_flag, c->gf, s));
+    c->launches += 2;
+    int flag = 0;
+    CK(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    if (flag) return fail_msg(RSGPU_ESINGULAR, "the chosen survivors give a singular matrix");
+    if ((rc = plan_build_tables(c, c->dec_full, s)) != RSGPU_OK) return rc;
+
+    if (c->n_erased > 0) {
+        if (c->dec_erased.rows != c->n_erased || !c->dec_erased.d_matrix)
+            if ((rc = plan_alloc(c->dec_erased, c->n_erased, k)) != RSGPU_OK) return rc;
+        // rows of the inverse that rebuild the erased natives
+        CK(cudaMemcpyAsync(c->d_rows, c->erased, sizeof(int) * c->n_erased, cudaMemcpyHostToDevice, s));
+        CK(launch_gather_rows(c->dec_full.d_matrix, k, c->d_rows, c->n_erased, c->dec_erased.d_matrix, s));
+        ++c->launches;
+        if ((rc = plan_build_tables(c, c->dec_erased, s)) != RSGPU_OK) return rc;
+    }
+    CK(cudaStreamSynchronize(s));
+    c->have_survivors = true;
+    return RSGPU_OK;
+}
+
+int rsgpu_get_decode_matrix(rsgpu_ctx *c, uint8_t *inverse)
+{
+    if (!c || !inverse) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (!c->have_survivors) return fail_msg(RSGPU_ESTATE, "rsgpu_set_survivors has not succeeded yet");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    CK(cudaMemcpy(inverse, c->dec_full.d_matrix, (size_t)c->k * c->k, cudaMemcpyDeviceToHost));
+    return RSGPU_OK;
+}
+
+int rsgpu_get_erased(rsgpu_ctx *c, int *idx, int *count)
+{
+    if (!c || !idx || !count) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (!c->have_survivors) return fail_msg(RSGPU_ESTATE, "rsgpu_set_survivors has not succeeded yet");
+    *count = c->n_erased;
+    memcpy(idx, c->erased, sizeof(int) * c->n_erased);
+    return RSGPU_OK;
+}
+
+int rsgpu_decode(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, uint8_t *nat_d, size_t nat_pitch,
+                 size_t len, void *stream)
+{
+    if (!c || !surv_d || !nat_d) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (!c->have_survivors) return fail_msg(RSGPU_ESTATE, "rsgpu_set_survivors has not succeeded yet");
+    if (c->k > 1 && (surv_pitch < len || nat_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    return plan_apply(c, c->dec_full, surv_d, surv_pitch, nat_d, nat_pitch, len, (cudaStream_t)stream);
+}
+
+int rsgpu_decode_erased(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, uint8_t *out_d, size_t out_pitch,
+                        size_t len, void *stream)
+{
+    if (!c || !surv_d) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (!c->have_survivors) return fail_msg(RSGPU_ESTATE, "rsgpu_set_survivors has not succeeded yet");
+    if (c->n_erased == 0) return RSGPU_OK;
+    if (!out_d) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if ((c->k > 1 && surv_pitch < len) || (c->n_erased > 1 && out_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    return plan_apply(c, c->dec_erased, surv_d, surv_pitch, out_d, out_pitch, len, (cudaStream_t)stream);
+}
+
+int rsgpu_invert_matrix(rsgpu_ctx *c, const uint8_t *matrix, uint8_t *inverse, int n)
+{
+    if (!c || !matrix || !inverse) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (n < 1 || n > 255) return fail_msg(RSGPU_EINVAL, "need 1 <= n <= 255");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    uint8_t *d = nullptr;
+    CK(cudaMalloc(&d, (size_t)2 * n * n));
+    cudaStream_t s = c->setup_stream;
+    int flag = 0;
+    cudaError_t e = cudaMemcpyAsync(d, matrix, (size_t)n * n, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) e = launch_gj_invert(d, d + (size_t)n * n, n, c->d_flag, c->gf, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(inverse, d + (size_t)n * n, (size_t)n * n, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail_cuda(e, "rsgpu_invert_matrix");
+    ++c->launches;
+    if (flag) return fail_msg(RSGPU_ESINGULAR, "matrix is singular");
+    return RSGPU_OK;
+}
+
+int rsgpu_matmul(rsgpu_ctx *c, const uint8_t *matrix, int rows, const uint8_t *in_d, size_t in_pitch,
+                 uint8_t *out_d, size_t out_pitch, size_t len, void *stream)
+{
+    if (!c || !matrix || !in_d || !out_d) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (rows < 1 || rows > 255) return fail_msg(RSGPU_EINVAL, "need 1 <= rows <= 255");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    if (c->scratch.rows != rows || !c->scratch.d_matrix)
+        if ((rc = plan_alloc(c->scratch, rows, c->k)) != RSGPU_OK) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    CK(cudaMemcpyAsync(c->scratch.d_matrix, matrix, (size_t)rows * c->k, cudaMemcpyHostToDevice, s));
+    if ((rc = plan_build_tables(c, c->scratch, s)) != RSGPU_OK) return rc;
+    if ((rc = plan_apply(c, c->scratch, in_d, in_pitch, out_d, out_pitch, len, s)) != RSGPU_OK) return rc;
+    CK(cudaStreamSynchronize(s));
+    return RSGPU_OK;
+}
+
+int rsgpu_host_alloc(void **ptr, size_t bytes)
+{
+    if (!ptr) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    *ptr = nullptr;
+    cudaError_t e = cudaMallocHost(ptr, bytes ? bytes : 1);
+    if (e == cudaErrorMemoryAllocation) return fail_msg(RSGPU_ENOMEM, "pinned allocation failed");
+    if (e != cudaSuccess) return fail_cuda(e, "cudaMallocHost");
+    return RSGPU_OK;
+}
+
+int rsgpu_host_free(void *ptr)
+{
+    if (ptr) CK(cudaFreeHost(ptr));
+    return RSGPU_OK;
+}
+
+int rsgpu_host_register(void *ptr, size_t bytes)
+{
+    if (!ptr) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    CK(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return RSGPU_OK;
+}
+
+int rsgpu_host_unregister(void *ptr)
+{
+    if (ptr) CK(cudaHostUnregister(ptr));
+    return RSGPU_OK;
+}
+
+int rsgpu_dev_alloc(rsgpu_ctx *c, void **ptr, size_t bytes)
+{
+    if (!c || !ptr) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    *ptr = nullptr;
+    cudaError_t e = cudaMalloc(ptr, bytes ? bytes : 1);
+    if (e == cudaErrorMemoryAllocation) return fail_msg(RSGPU_ENOMEM, "device allocation failed");
+    if (e != cudaSuccess) return fail_cuda(e, "cudaMalloc");
+    return RSGPU_OK;
+}
+
+int rsgpu_dev_free(rsgpu_ctx *c, void *ptr)
+{
+    if (!c) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    if (ptr) CK(cudaFree(ptr));
+    return RSGPU_OK;
+}
+
+int rsgpu_memcpy_h2d(rsgpu_ctx *c, void *dst_d, const void *src, size_t bytes)
+{
+    if (!c) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    CK(cudaMemcpy(dst_d, src, bytes, cudaMemcpyHostToDevice));
+    return RSGPU_OK;
+}
+
+int rsgpu_memcpy_d2h(rsgpu_ctx *c, void *dst, const void *src_d, size_t bytes)
+{
+    if (!c) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    CK(cudaMemcpy(dst, src_d, bytes, cudaMemcpyDeviceToHost));
+    return RSGPU_OK;
+}
+
+int rsgpu_sync(rsgpu_ctx *c)
+{
+    if (!c) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    CK(cudaDeviceSynchronize());
+    return RSGPU_OK;
+}
+
+int rsgpu_set_tuning(rsgpu_ctx *c, int variant, int threads, int max_blocks)
+{
+    if (!c) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (threads < 0 || threads > 256 || (threads % 32) != 0) return fail_msg(RSGPU_EINVAL, "threads must be a multiple of 32, <= 256");
+    if (variant < 0 || max_blocks < 0) return fail_msg(RSGPU_EINVAL, "negative tuning value");
+    c->tune.variant = variant;
+    c->tune.threads = threads;
+    c->tune.max_blocks = max_blocks;
+    return RSGPU_OK;
+}
+
+}  // extern "C"

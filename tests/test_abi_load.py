@@ -1,0 +1,42 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads and exports every symbol that
+include/rsgpu.h declares; without a GPU the entry points fail loudly (no CPU fallback)."""
+import os
+import re
+
+import pytest
+
+from gpu_lib import ROOT, rs
+
+
+def _declared_symbols(header):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rsgpu_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    if not os.path.exists(rs.LIB_PATH):
+        rs.build()
+    L = rs.lib()
+    declared = _declared_symbols("rsgpu.h")
+    assert len(declared) >= 25
+    for name in declared:
+        assert hasattr(L, name), f"{name} declared in include/rsgpu.h but not exported by librsgpu.so"
+    assert sorted(rs.ABI_SYMBOLS) == [s for s in declared if s in rs.ABI_SYMBOLS]
+    missing_in_py = set(declared) - set(rs.ABI_SYMBOLS)
+    assert not missing_in_py, f"python mirror lacks {missing_in_py}"
+
+
+def test_strerror_codes():
+    L = rs.lib()
+    assert L.rsgpu_strerror(0) == b"ok"
+    assert b"singular" in L.rsgpu_strerror(rs.RSGPU_ESINGULAR)
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(rs.RSGPUError) as ei:
+        rs.RSContext(4, 2)
+    assert ei.value.code == rs.RSGPU_ECUDA

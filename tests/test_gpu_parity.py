@@ -1,0 +1,405 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes), against the CPU oracle on the
+same seeded inputs and against the golden fixtures made from the reference's own cpu-rs.c.
+Bit-exact everywhere: the arithmetic is integer GF(2^8)."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle_lib import Oracle
+from rsdata import pattern_bytes, splitmix64_bytes
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = json.load(open(os.path.join(HERE, "golden", "golden.json")))
+
+
+def sha(b):
+    return hashlib.sha256(bytes(b)).hexdigest()
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch as t
+    if not t.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return t
+
+
+@pytest.fixture(scope="module")
+def rs(torch):
+    from gpu_lib import rs as m
+    m.lib()  # raises if librsgpu.so is missing: no fallback
+    return m
+
+
+@pytest.fixture(scope="module")
+def orc():
+    return Oracle()
+
+
+def gf_rank(orc, M):
+    """Rank over GF(2^8) by plain row reduction with the oracle's field ops (test-side check only)."""
+    A = [list(map(int, r)) for r in M]
+    n, m, rank = len(A), len(A[0]), 0
+    for c in range(m):
+        piv = next((r for r in range(rank, n) if A[r][c]), None)
+        if piv is None:
+            continue
+        A[rank], A[piv] = A[piv], A[rank]
+        inv = orc.gf_div(1, A[rank][c])
+        A[rank] = [orc.gf_mul(inv, x) for x in A[rank]]
+        for r in range(n):
+            if r != rank and A[r][c]:
+                f = A[r][c]
+                A[r] = [x ^ orc.gf_mul(f, y) for x, y in zip(A[r], A[rank])]
+        rank += 1
+    return rank
+
+
+def to_dev(torch, a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def gpu_encode(torch, ctx, data, pitch=None, out_pitch=None, in_off=0, out_off=0):
+    """data: (k, L) uint8 host array -> (p, L) parity computed on the GPU via rsgpu_encode."""
+    k, L = data.shape
+    pitch = pitch or L
+    out_pitch = out_pitch or L
+    buf = torch.zeros(k * pitch + in_off + 64, dtype=torch.uint8, device="cuda")
+    view = buf[in_off:in_off + k * pitch].view(k, pitch)
+    view[:, :L] = to_dev(torch, data)
+    out = torch.full((ctx.p * out_pitch + out_off + 64,), 0xEE, dtype=torch.uint8, device="cuda")
+    ctx.encode(buf.data_ptr() + in_off, pitch, out.data_ptr() + out_off, out_pitch, L,
+               torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    res = out[out_off:out_off + ctx.p * out_pitch].view(ctx.p, out_pitch)
+    if out_pitch > L:  # bytes between rows must be untouched
+        assert bool((res[:, L:] == 0xEE).all())
+    return res[:, :L].cpu().numpy()
+
+
+# ---- matrices -----------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("k,p", [(4, 2), (10, 4), (16, 4), (32, 8), (5, 3), (20, 12), (64, 2), (128, 3), (255, 1), (1, 1), (17, 0)])
+def test_total_matrix_vs_oracle(rs, orc, k, p):
+    with rs.RSContext(k, p) as ctx:
+        T = ctx.total_matrix()
+    assert (T == orc.gen_total_encoding_matrix(k, p)).all()
+    key = f"{k},{p}"
+    if key in GOLD["vandermonde"]:
+        assert T[k:].tobytes().hex() == GOLD["vandermonde"][key]
+
+
+def test_create_rejects_bad_arguments(rs):
+    for k, p in [(0, 2), (256, 1), (4, -1), (4, 256)]:
+        with pytest.raises(rs.RSGPUError) as ei:
+            rs.RSContext(k, p)
+        assert ei.value.code == rs.RSGPU_EINVAL
+    with pytest.raises(rs.RSGPUError):
+        rs.RSContext(4, 2, device=99)
+
+
+# ---- encode -------------------------------------------------------------------------------------
+
+ENC_SHAPES = [
+    (4, 2, 1), (4, 2, 15), (4, 2, 16), (4, 2, 17), (10, 4, 8), (10, 4, 4096), (10, 4, 100_003),
+    (16, 4, 65_536 + 48), (32, 8, 30_011), (5, 3, 4097), (6, 6, 70_001), (20, 12, 5_021), (3, 1, 777),
+    (11, 4, 9_999), (13, 5, 12_345), (22, 7, 3_333), (1, 4, 1000), (64, 2, 2048), (255, 8, 512), (9, 16, 1600),
+]
+
+
+@pytest.mark.parametrize("k,p,L", ENC_SHAPES)
+def test_encode_vs_oracle(rs, orc, torch, k, p, L):
+    data = splitmix64_bytes(1000 + k * 31 + p, k * L).reshape(k, L)
+    with rs.RSContext(k, p) as ctx:
+        got = gpu_encode(torch, ctx, data)
+    want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)
+    assert (got == want).all()
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2])
+@pytest.mark.parametrize("k,p,L", [(10, 4, 200_000), (32, 8, 50_000), (11, 3, 40_001)])
+def test_encode_variants_vs_oracle(rs, orc, torch, variant, k, p, L):
+    data = splitmix64_bytes(77 + variant, k * L).reshape(k, L)
+    with rs.RSContext(k, p) as ctx:
+        ctx.set_tuning(variant=variant)
+        got = gpu_encode(torch, ctx, data)
+    assert (got == orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)).all()
+
+
+def test_encode_pitch_and_misalignment(rs, orc, torch):
+    k, p, L = 10, 4, 10_007
+    data = splitmix64_bytes(5, k * L).reshape(k, L)
+    want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)
+    with rs.RSContext(k, p) as ctx:
+        assert (gpu_encode(torch, ctx, data, pitch=10_240, out_pitch=12_288) == want).all()   # aligned pitches
+        assert (gpu_encode(torch, ctx, data, pitch=10_009, out_pitch=10_011) == want).all()   # odd pitches -> byte path
+        assert (gpu_encode(torch, ctx, data, pitch=10_240, out_pitch=10_240, in_off=3) == want).all()
+        assert (gpu_encode(torch, ctx, data, pitch=10_240, out_pitch=10_240, out_off=5) == want).all()
+
+
+def test_encode_overwrites_and_zero_len(rs, torch):
+    with rs.RSContext(4, 2) as ctx:
+        d = torch.zeros(4 * 64, dtype=torch.uint8, device="cuda")
+        out = torch.full((2 * 64,), 0x55, dtype=torch.uint8, device="cuda")
+        ctx.encode(d, 64, out, 64, 0)          # empty input: nothing written, no error
+        torch.cuda.synchronize()
+        assert bool((out == 0x55).all())
+        ctx.encode(d, 64, out, 64, 64)         # zero data -> zero parity even though out was dirty
+        torch.cuda.synchronize()
+        assert bool((out == 0).all())
+        with pytest.raises(rs.RSGPUError):
+            ctx.encode(d, 32, out, 64, 64)     # pitch < len
+
+
+@pytest.mark.parametrize("ci", range(len(GOLD["encode"])))
+def test_encode_golden_fragments(rs, torch, ci):
+    """Same file split as cpu-rs.c encode_file (zero-padded last native), parity fragments hashed."""
+    spec = GOLD["encode"][ci]
+    k, p, L = spec["k"], spec["p"], spec["chunk"]
+    raw = pattern_bytes(spec["mul"], spec["add"], spec["nbytes"]) if spec["gen"] == "pattern" \
+        else splitmix64_bytes(spec["seed"], spec["nbytes"])
+    data = np.zeros(k * L, np.uint8)
+    data[:spec["nbytes"]] = raw
+    data = data.reshape(k, L)
+    with rs.RSContext(k, p) as ctx:
+        got = gpu_encode(torch, ctx, data)
+    for i in range(k):
+        assert sha(data[i].tobytes()) == spec["fragment_sha256"][i]
+    for i in range(p):
+        assert sha(got[i].tobytes()) == spec["fragment_sha256"][k + i], f"parity {i}"
+        if "fragment_hex" in spec:
+            assert got[i].tobytes().hex() == spec["fragment_hex"][k + i]
+
+
+# ---- inverse ------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("case", GOLD["inverse"] + GOLD["inverse_natural_rs46"],
+                         ids=lambda c: f"k{c['k']}-{'_'.join(map(str, c['order'][:5]))}")
+def test_inverse_vs_golden(rs, orc, case):
+    k, p = case["k"], case["p"]
+    with rs.RSContext(k, p) as ctx:
+        ctx.set_survivors(case["order"])
+        inv = ctx.decode_matrix()
+    if case.get("is_true_inverse", True):
+        assert inv.tobytes().hex() == case["inverse"]      # unique inverse: same bytes as the reference
+    sub = orc.gen_total_encoding_matrix(k, p)[case["order"]]
+    assert (orc.matrix_mul(sub, inv) == np.eye(k, dtype=np.uint8)).all()
+
+
+def test_inverse_kats_from_reference_docs(rs):
+    with rs.RSContext(4, 2) as ctx:
+        M = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [1, 2, 3, 4], [1, 1, 1, 1]], np.uint8)   # doc/slide.tex:501-557
+        assert ctx.invert_matrix(M).tolist() == [[1, 0, 0, 0], [0, 1, 0, 0], [104, 187, 186, 210], [105, 186, 186, 211]]
+        M = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [1, 1, 1, 1], [1, 2, 3, 4]], np.uint8)   # src/decode-gj.cu:1282,1453
+        assert ctx.invert_matrix(M).tolist() == [[1, 0, 0, 0], [0, 1, 0, 0], [104, 187, 210, 186], [105, 186, 211, 186]]
+
+
+def test_inverse_random_orders_true_inverse(rs, orc):
+    """Any survivor ORDER, also those where the reference's column swap goes wrong: A * inv == I; and
+    bit-identical to the oracle wherever the oracle reports the reference-correct domain."""
+    rng = np.random.default_rng(3)
+    for k, p in [(4, 2), (10, 4), (16, 4), (32, 8)]:
+        T = orc.gen_total_encoding_matrix(k, p)
+        with rs.RSContext(k, p) as ctx:
+            n_ok = n_same = 0
+            for _ in range(60):
+                order = rng.permutation(k + p)[:k].tolist()
+                try:
+                    ctx.set_survivors(order)
+                except rs.SingularError:
+                    assert gf_rank(orc, T[order]) < k      # independently confirmed singular
+                    continue
+                inv = ctx.decode_matrix()
+                assert (orc.matrix_mul(T[order], inv) == np.eye(k, dtype=np.uint8)).all()
+                n_ok += 1
+                ref_inv, st = orc.invert_matrix(T[order])
+                if st == 0:
+                    assert (inv == ref_inv).all()
+                    n_same += 1
+            assert n_ok >= 40
+
+
+def test_inverse_large_random_matrices(rs, orc):
+    rng = np.random.default_rng(11)
+    with rs.RSContext(4, 2) as ctx:
+        for n in (1, 2, 7, 33, 100, 255):
+            M = rng.integers(0, 256, (n, n), dtype=np.uint8)
+            try:
+                inv = ctx.invert_matrix(M)
+            except rs.SingularError:
+                continue
+            assert (orc.matrix_mul(M, inv) == np.eye(n, dtype=np.uint8)).all()
+
+
+def test_singular_survivor_sets_are_reported(rs):
+    # [I;V] is not MDS; RS(10,14) erasing natives {0,1,2} and parity 12 is singular
+    k, p = 10, 4
+    with rs.RSContext(k, p) as ctx:
+        for erased in [(0, 1, 2, 12), (0, 3, 4, 12), (4, 5, 9, 11)]:
+            surv = [i for i in range(k + p) if i not in erased]
+            with pytest.raises(rs.SingularError):
+                ctx.set_survivors(surv)
+        ctx.set_survivors([i for i in range(14) if i not in (0, 1, 2, 3)])   # fine again afterwards
+    with rs.RSContext(4, 2) as ctx:
+        with pytest.raises(rs.SingularError):
+            ctx.invert_matrix(np.array([[1, 2, 0, 0], [2, 4, 0, 0], [0, 0, 1, 0], [0, 0, 0, 1]], np.uint8))
+        with pytest.raises(rs.RSGPUError):
+            ctx.set_survivors([0, 1, 2, 9])      # index out of range
+        d = ctx.dev_alloc(64)
+        with pytest.raises(rs.RSGPUError) as ei:  # decode before a successful set_survivors
+            rs.RSContext(4, 2).decode(d, 16, d, 16, 16)
+        assert ei.value.code == rs.RSGPU_ESTATE
+        ctx.dev_free(d)
+
+
+# ---- decode -------------------------------------------------------------------------------------
+
+DEC_CASES = [
+    (4, 2, [0, 1, 4, 5], 16_777),
+    (4, 2, [2, 3, 4, 5], 4_099),            # the unit-test.sh order: reference decodes this WRONG, we must not
+    (4, 2, [0, 1, 3, 5], 1_000),            # ditto
+    (10, 4, [10, 11, 12, 13, 4, 5, 6, 7, 8, 9], 100_003),
+    (10, 4, [0, 1, 2, 10, 4, 5, 11, 7, 8, 13], 33_333),
+    (16, 4, [16, 17, 18, 19] + list(range(4, 16)), 20_480),
+    (32, 8, list(range(32, 40)) + list(range(8, 32)), 9_001),
+    (5, 3, [7, 6, 5, 4, 3], 2_222),
+    (10, 4, list(range(10)), 5_000),        # nothing erased
+]
+
+
+@pytest.mark.parametrize("k,p,order,L", DEC_CASES, ids=lambda v: str(v)[:24])
+def test_decode_roundtrip_and_oracle(rs, orc, torch, k, p, order, L):
+    data = splitmix64_bytes(4242 + k, k * L).reshape(k, L)
+    V = orc.gen_encoding_matrix(p, k)
+    frags = np.concatenate([data, orc.matrix_mul(V, data)], axis=0)       # oracle-encoded stripe
+    surv = np.ascontiguousarray(frags[order])
+    with rs.RSContext(k, p) as ctx:
+        ctx.set_survivors(order)
+        d_surv = to_dev(torch, surv)
+        out = torch.empty((k, L), dtype=torch.uint8, device="cuda")
+        ctx.decode(d_surv, L, out, L, L, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        assert (out.cpu().numpy() == data).all()
+        # reference-semantic result == oracle's matrix_mul with the oracle's inverse where that is right
+        ref_inv, st = orc.invert_matrix(orc.gen_total_encoding_matrix(k, p)[order])
+        if st == 0:
+            assert (orc.matrix_mul(ref_inv, surv) == out.cpu().numpy()).all()
+        erased = ctx.erased()
+        assert erased == sorted(set(range(k)) - set(i for i in order if i < k))
+        if erased:
+            out_e = torch.empty((len(erased), L), dtype=torch.uint8, device="cuda")
+            ctx.decode_erased(d_surv, L, out_e, L, L, torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+            assert (out_e.cpu().numpy() == data[erased]).all()
+
+
+def test_gpu_encode_then_gpu_decode_all_double_erasures_rs46(rs, torch):
+    k, p, L = 4, 2, 3_001
+    data = splitmix64_bytes(9, k * L).reshape(k, L)
+    with rs.RSContext(k, p) as ctx:
+        parity = gpu_encode(torch, ctx, data)
+        frags = np.concatenate([data, parity], axis=0)
+        import itertools
+        for lost in itertools.combinations(range(k + p), 2):
+            order = [i for i in range(k + p) if i not in lost][:k]
+            ctx.set_survivors(order)
+            d_surv = to_dev(torch, frags[order])
+            out = torch.empty((k, L), dtype=torch.uint8, device="cuda")
+            ctx.decode(d_surv, L, out, L, L)
+            torch.cuda.synchronize()
+            assert (out.cpu().numpy() == data).all(), lost
+
+
+# ---- generic matmul, many rows (several row groups) -------------------------------------------
+
+@pytest.mark.parametrize("rows,k,L", [(1, 10, 1000), (4, 10, 1000), (5, 10, 1000), (8, 7, 4000), (9, 16, 2049),
+                                        (20, 12, 3000), (40, 32, 1111), (255, 3, 300)])
+def test_generic_matmul_vs_oracle(rs, orc, torch, rows, k, L):
+    rng = np.random.default_rng(rows * 100 + k)
+    M = rng.integers(0, 256, (rows, k), dtype=np.uint8)
+    B = rng.integers(0, 256, (k, L), dtype=np.uint8)
+    with rs.RSContext(k, 1) as ctx:
+        d_in = to_dev(torch, B)
+        out = torch.empty((rows, L), dtype=torch.uint8, device="cuda")
+        ctx.matmul(M, d_in, L, out, L, L)
+        assert (out.cpu().numpy() == orc.matrix_mul(M, B)).all()
+
+
+# ---- host-memory pipeline ------------------------------------------------------------------------
+
+@pytest.mark.parametrize("k,p,L,slots", [(4, 2, 5_000_001, 3), (10, 4, 3_000_000, 4), (32, 8, 700_003, 2), (10, 4, 100, 1)])
+def test_host_pipeline_vs_oracle(rs, orc, torch, k, p, L, slots):
+    data = splitmix64_bytes(31 + k, k * L).reshape(k, L)
+    want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)
+    pin_in = torch.from_numpy(data).pin_memory()
+    pin_out = torch.empty((p, L), dtype=torch.uint8).pin_memory()
+    with rs.RSContext(k, p) as ctx:
+        ctx.encode_host(pin_in.data_ptr(), L, pin_out.data_ptr(), L, L, slots)
+        assert (pin_out.numpy() == want).all()
+        # pageable buffers work too (slower)
+        out2 = np.zeros((p, L), np.uint8)
+        ctx.encode_host(data, L, out2, L, L, slots)
+        assert (out2 == want).all()
+        # decode through the pipeline
+        frags = np.concatenate([data, want], axis=0)
+        order = list(range(k, k + p)) + list(range(p, k)) if p <= k else list(range(k))
+        ctx.set_survivors(order)
+        surv = np.ascontiguousarray(frags[order])
+        back = np.zeros((k, L), np.uint8)
+        ctx.decode_host(surv, L, back, L, L, slots)
+        assert (back == data).all()
+
+
+# ---- full-size, size-independent properties (BASELINE configs are too big for the oracle) ----------
+
+def test_large_roundtrip_and_linearity_rs10_14(rs, torch):
+    k, p = 10, 4
+    L = 64 << 20                                # 64 MiB per fragment: 640 MiB in, 256 MiB parity
+    g = torch.Generator(device="cuda").manual_seed(1)
+    a = torch.randint(0, 256, (k, L), dtype=torch.uint8, device="cuda", generator=g)
+    b = torch.randint(0, 256, (k, L), dtype=torch.uint8, device="cuda", generator=g)
+    st = torch.cuda.current_stream().cuda_stream
+    with rs.RSContext(k, p) as ctx:
+        pa = torch.empty((p, L), dtype=torch.uint8, device="cuda")
+        pb = torch.empty_like(pa)
+        pab = torch.empty_like(pa)
+        ctx.encode(a, L, pa, L, L, st)
+        ctx.encode(b, L, pb, L, L, st)
+        ctx.encode(a ^ b, L, pab, L, L, st)
+        torch.cuda.synchronize()
+        assert bool(((pa ^ pb) == pab).all())                       # linearity over GF(2)
+        x = a[0].clone()
+        for j in range(1, k):
+            x ^= a[j]
+        assert bool((pa[0] == x).all())                             # row 0 of V is all ones: plain XOR
+        # encode -> erase 4 natives -> decode
+        order = [10, 11, 12, 13, 4, 5, 6, 7, 8, 9]
+        ctx.set_survivors(order)
+        surv = torch.cat([pa, a[4:]], dim=0).contiguous()
+        out = torch.empty((4, L), dtype=torch.uint8, device="cuda")
+        ctx.decode_erased(surv, L, out, L, L, st)
+        torch.cuda.synchronize()
+        assert bool((out == a[:4]).all())
+
+
+def test_sampled_windows_vs_oracle_large(rs, orc, torch):
+    """Columns are independent: check head, tail and random 4 KiB windows of a large stripe with the oracle."""
+    k, p = 16, 4
+    L = (32 << 20) + 16 * 7 + 5                 # not a multiple of 16: exercises the tail kernel too
+    g = torch.Generator(device="cuda").manual_seed(2)
+    a = torch.randint(0, 256, (k, L), dtype=torch.uint8, device="cuda", generator=g)
+    with rs.RSContext(k, p) as ctx:
+        out = torch.empty((p, L), dtype=torch.uint8, device="cuda")
+        ctx.encode(a, L, out, L, L, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+    V = orc.gen_encoding_matrix(p, k)
+    rng = np.random.default_rng(4)
+    starts = [0, L - 4096] + [int(s) for s in rng.integers(0, L - 4096, 30)]
+    for s in starts:
+        win = a[:, s:s + 4096].cpu().numpy()
+        assert (out[:, s:s + 4096].cpu().numpy() == orc.matrix_mul(V, win)).all(), s
