@@ -72,38 +72,51 @@ template <> __device__ __forceinline__ void acc_clear<8>(Acc<8> &acc)
     for (int i = 0; i < 16; ++i) { acc.a[i] = 0; acc.b[i] = 0; }
 }
 
-// Scaled table offsets (index * W) of the 8 nibbles of one 32-bit data word.
-// EX = 0: shift + mask per nibble.  EX = 1: two masks per word, PRMT byte extract per nibble.
-// EX = 2: two masks per word, DP4A byte extract that also adds the table base.
+// Shared-memory layout: fragment j owns the 256-byte page at tb + 256*j (tb is 256-byte aligned);
+// its low-nibble table (16 entries of W bytes) sits at +0 and its high-nibble table at +16*W.
+//
+// The 8 lookup addresses of one 32-bit data word.  Two masked copies of the word hold the scaled
+// nibbles (nibble * W) of all four bytes; what differs between the variants is how one byte of those
+// is turned into an address:
+// EX = 0: one PRMT per lookup splices the byte into the page-base register (page bases have
+//          a zero low byte), so the address costs a single alu-pipe instruction and the LDS needs no
+//          immediate.  The +16*W of the high table is OR-ed into the mask step.
+// EX = 1: shift + mask per nibble, then an add of the page base.
+// EX = 2 (default): one DP4A per lookup (dot product with a one-hot byte selector, accumulating onto the base).
+// EX = 3: low nibbles as EX 0, high nibbles as EX 2 -- splits the work over two pipes.
 template <int W, int EX>
-__device__ __forceinline__ void mac_word(uint32_t w, uint32_t tlo, uint32_t thi, Acc<W> &acc, int pos0)
+__device__ __forceinline__ void mac_word(uint32_t w, uint32_t tj, uint32_t hi4, Acc<W> &acc, int pos0)
 {
     constexpr int SH = (W == 4) ? 2 : 3;            // log2(W)
     constexpr uint32_t M1 = 0xFu << SH;             // one scaled nibble
     constexpr uint32_t M4 = M1 * 0x01010101u;       // four of them
+    constexpr uint32_t HI1 = 16u * W;               // offset of the high-nibble table inside the page
     uint32_t olo[4], ohi[4];
-    if constexpr (EX == 0) {
+    if constexpr (EX == 1) {
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
             // low nibble of byte b sits at bit 8b, wanted at bit SH: shift right by 8b-SH (left for b = 0)
             const uint32_t lo = (b == 0) ? (w << SH) : (w >> (8 * b - SH));
-            olo[b] = tlo + (lo & M1);
-            ohi[b] = thi + ((w >> (8 * b + 4 - SH)) & M1);
+            olo[b] = tj + (lo & M1);
+            ohi[b] = tj + HI1 + ((w >> (8 * b + 4 - SH)) & M1);
         }
     } else {
         const uint32_t wl = (w << SH) & M4;
-        const uint32_t wh = (w >> (4 - SH)) & M4;
-        if constexpr (EX == 1) {
+        if constexpr (EX == 0) {
+            // hi4 == HI4, but it arrives as a kernel argument: a value the compiler cannot fold keeps
+            // (x & M4) | hi4 as ONE three-input LOP3 instead of an AND-immediate plus an OR-immediate
+            const uint32_t wh = ((w >> (4 - SH)) & M4) | hi4;
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
-                olo[b] = tlo + __byte_perm(wl, 0u, 0x4440u + b);
-                ohi[b] = thi + __byte_perm(wh, 0u, 0x4440u + b);
+                olo[b] = __byte_perm(wl, tj, 0x7650u + b);
+                ohi[b] = __byte_perm(wh, tj, 0x7650u + b);
             }
         } else {
+            const uint32_t wh = (w >> (4 - SH)) & M4;
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
-                olo[b] = __dp4a(wl, 1u << (8 * b), tlo);
-                ohi[b] = __dp4a(wh, 1u << (8 * b), thi);
+                olo[b] = (EX == 2) ? __dp4a(wl, 1u << (8 * b), tj) : __byte_perm(wl, tj, 0x7650u + b);
+                ohi[b] = __dp4a(wh, 1u << (8 * b), tj + HI1);
             }
         }
     }
@@ -120,13 +133,12 @@ __device__ __forceinline__ void mac_word(uint32_t w, uint32_t tlo, uint32_t thi,
 }
 
 template <int W, int EX>
-__device__ __forceinline__ void mac_vec(const uint4 &d, uint32_t tj, Acc<W> &acc)
+__device__ __forceinline__ void mac_vec(const uint4 &d, uint32_t tj, uint32_t hi4, Acc<W> &acc)
 {
-    const uint32_t tlo = tj, thi = tj + 16 * W;
-    mac_word<W, EX>(d.x, tlo, thi, acc, 0);
-    mac_word<W, EX>(d.y, tlo, thi, acc, 4);
-    mac_word<W, EX>(d.z, tlo, thi, acc, 8);
-    mac_word<W, EX>(d.w, tlo, thi, acc, 12);
+    mac_word<W, EX>(d.x, tj, hi4, acc, 0);
+    mac_word<W, EX>(d.y, tj, hi4, acc, 4);
+    mac_word<W, EX>(d.z, tj, hi4, acc, 8);
+    mac_word<W, EX>(d.w, tj, hi4, acc, 12);
 }
 
 // 16 accumulator words (byte r = row r) -> 4 row vectors of 16 bytes.
@@ -150,35 +162,52 @@ __device__ __forceinline__ void transpose_store(const uint32_t *a, uint8_t *out,
             stg_stream(out + (size_t)(row0 + i) * out_pitch + off, make_uint4(r[i][0], r[i][1], r[i][2], r[i][3]));
 }
 
-template <int JB>
-__device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *in, size_t in_pitch, size_t off,
-                                           int j0, int k)
+// Load one batch of JB fragment vectors through a running pointer (q += pitch per fragment: two adds
+// instead of a 64-bit multiply-add chain per load).  PAD: the last batch may run past fragment k-1;
+// padded slots re-read the last valid row (their tables are all zero).
+template <int JB, bool PAD>
+__device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *&q, size_t in_pitch, int &j, int k)
 {
 #pragma unroll
     for (int jj = 0; jj < JB; ++jj) {
-        int j = j0 + jj;
-        j = j < k ? j : k - 1;     // padded fragments re-read a valid row; their tables are all zero
-        d[jj] = ldg_stream(in + (size_t)j * in_pitch + off);
+        d[jj] = ldg_stream(q);
+        if constexpr (PAD) {
+            ++j;
+            if (j < k) q += in_pitch;
+        } else {
+            q += in_pitch;
+        }
     }
 }
 
 // W: table entry bytes (4: up to 4 output rows, 8: up to 8).  JB: fragments per load batch.
-// kb = number of batches (kb*JB >= k, kb*JB <= kpad).
-template <int W, int JB, int EX>
+// kb = number of batches (kb*JB >= k, kb*JB <= kpad); PAD = (kb*JB > k).
+template <int W, int JB, int EX, bool PAD>
 __global__ void __launch_bounds__(256)
 k_gf_matmul(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
-            const uint32_t *__restrict__ tab, int tab_vec4, int k, int kb, int nrows, size_t nvec)
+            const uint32_t *__restrict__ tab, int npages, int k, int kb, int nrows, size_t nvec, uint32_t hi4)
 {
-    extern __shared__ __align__(16) uint32_t s_tab[];
-    for (int i = threadIdx.x; i < tab_vec4; i += blockDim.x)
-        reinterpret_cast<uint4 *>(s_tab)[i] = reinterpret_cast<const uint4 *>(tab)[i];
+    // one 256-byte page per fragment (see mac_word); the launcher adds 256 bytes of slack so the base
+    // can be rounded up to a 256-byte boundary whatever offset the dynamic window starts at
+    extern __shared__ __align__(16) uint8_t s_raw[];
+    const uint32_t tb = ((uint32_t)__cvta_generic_to_shared(s_raw) + 255u) & ~255u;
+    {
+        constexpr int V4 = 32 * W / 16;   // uint4 per fragment in the global table (lo + hi tables)
+        for (int i = threadIdx.x; i < npages * V4; i += blockDim.x) {
+            const int j = i / V4, r = i - j * V4;
+            const uint4 t = reinterpret_cast<const uint4 *>(tab)[i];
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(tb + j * 256 + r * 16), "r"(t.x), "r"(t.y),
+                         "r"(t.z), "r"(t.w) : "memory");
+        }
+    }
     __syncthreads();
-    const uint32_t tb = (uint32_t)__cvta_generic_to_shared(s_tab);
 
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint4 nxt[JB];
-    if (v < nvec) load_batch<JB>(nxt, in, in_pitch, v * 16, 0, k);
+    const uint8_t *q = in + v * 16;
+    int j = 0;
+    if (v < nvec) load_batch<JB, PAD>(nxt, q, in_pitch, j, k);
 
     while (v < nvec) {
         Acc<W> acc;
@@ -188,13 +217,16 @@ k_gf_matmul(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict
             uint4 cur[JB];
 #pragma unroll
             for (int jj = 0; jj < JB; ++jj) cur[jj] = nxt[jj];
-            if (b + 1 < kb)
-                load_batch<JB>(nxt, in, in_pitch, v * 16, (b + 1) * JB, k);
-            else if (vn < nvec)
-                load_batch<JB>(nxt, in, in_pitch, vn * 16, 0, k);
-            const uint32_t t0 = tb + (uint32_t)(b * JB) * (32 * W);
+            if (b + 1 < kb) {
+                load_batch<JB, PAD>(nxt, q, in_pitch, j, k);
+            } else if (vn < nvec) {
+                q = in + vn * 16;
+                j = 0;
+                load_batch<JB, PAD>(nxt, q, in_pitch, j, k);
+            }
+            const uint32_t t0 = tb + (uint32_t)(b * JB) * 256u;
 #pragma unroll
-            for (int jj = 0; jj < JB; ++jj) mac_vec<W, EX>(cur[jj], t0 + jj * (32 * W), acc);
+            for (int jj = 0; jj < JB; ++jj) mac_vec<W, EX>(cur[jj], t0 + jj * 256u, hi4, acc);
         }
         transpose_store(acc.a, out, out_pitch, v * 16, 0, nrows);
         if constexpr (W == 8) transpose_store(acc.b, out, out_pitch, v * 16, 4, nrows - 4);
@@ -230,33 +262,35 @@ k_gf_matmul_bytes(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__re
     }
 }
 
-using MatmulFn = void (*)(const uint8_t *, size_t, uint8_t *, size_t, const uint32_t *, int, int, int, int, size_t);
+using MatmulFn = void (*)(const uint8_t *, size_t, uint8_t *, size_t, const uint32_t *, int, int, int, int, size_t, uint32_t);
 
 template <int W, int EX>
-MatmulFn pick_jb(int jb)
+MatmulFn pick_jb(int jb, bool pad)
 {
     switch (jb) {
-    case 1: return k_gf_matmul<W, 1, EX>;
-    case 2: return k_gf_matmul<W, 2, EX>;
-    case 3: return k_gf_matmul<W, 3, EX>;
-    case 4: return k_gf_matmul<W, 4, EX>;
-    case 5: return k_gf_matmul<W, 5, EX>;
-    case 6: return k_gf_matmul<W, 6, EX>;
-    case 7: return k_gf_matmul<W, 7, EX>;
-    default: return k_gf_matmul<W, 8, EX>;
+    case 1: return k_gf_matmul<W, 1, EX, false>;
+    case 2: return k_gf_matmul<W, 2, EX, false>;
+    case 3: return k_gf_matmul<W, 3, EX, false>;
+    case 4: return k_gf_matmul<W, 4, EX, false>;
+    case 5: return k_gf_matmul<W, 5, EX, false>;
+    case 6: return k_gf_matmul<W, 6, EX, false>;
+    case 7: return k_gf_matmul<W, 7, EX, false>;
+    default: return pad ? k_gf_matmul<W, 8, EX, true> : k_gf_matmul<W, 8, EX, false>;
     }
 }
 
-MatmulFn pick_kernel(int width, int jb, int ex)
+MatmulFn pick_kernel(int width, int jb, int ex, bool pad)
 {
     if (width == 4) {
-        if (ex == 1) return pick_jb<4, 1>(jb);
-        if (ex == 2) return pick_jb<4, 2>(jb);
-        return pick_jb<4, 0>(jb);
+        if (ex == 1) return pick_jb<4, 1>(jb, pad);
+        if (ex == 2) return pick_jb<4, 2>(jb, pad);
+        if (ex == 3) return pick_jb<4, 3>(jb, pad);
+        return pick_jb<4, 0>(jb, pad);
     }
-    if (ex == 1) return pick_jb<8, 1>(jb);
-    if (ex == 2) return pick_jb<8, 2>(jb);
-    return pick_jb<8, 0>(jb);
+    if (ex == 1) return pick_jb<8, 1>(jb, pad);
+    if (ex == 2) return pick_jb<8, 2>(jb, pad);
+    if (ex == 3) return pick_jb<8, 3>(jb, pad);
+    return pick_jb<8, 0>(jb, pad);
 }
 
 // Fragments per load batch: the largest divisor of k in 4..8 (no padded fragments), else 8 (or k).
@@ -284,9 +318,11 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
     if (nvec) {
         const int jb = choose_jb(k);
         const int kb = (k + jb - 1) / jb;           // kb*jb <= kpad because kpad is k rounded up to 8
-        const int ex = tune.variant % 10;
-        MatmulFn fn = pick_kernel(g.width, jb, ex);
-        const size_t smem = (size_t)kpad * 32 * g.width;
+        // variant 0 = default = DP4A extraction (EX 2): same speed as the PRMT splice on B200 but it
+        // leaves the alu pipe at 45% instead of 81% (ncu, profiles/r1_pipes.md); 1..4 select EX 0..3
+        const int ex = tune.variant == 0 ? 2 : (tune.variant - 1) % 4;
+        MatmulFn fn = pick_kernel(g.width, jb, ex, kb * jb > k);
+        const size_t smem = (size_t)kpad * 256 + 256;   // one page per fragment + alignment slack
         if (smem > 48 * 1024) {
             cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             if (e != cudaSuccess) return e;
@@ -299,7 +335,8 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
         size_t cap = (size_t)dev.sm_count * occ;
         if (tune.max_blocks > 0 && (size_t)tune.max_blocks < cap) cap = tune.max_blocks;
         const unsigned grid = (unsigned)(want < cap ? want : cap);
-        fn<<<grid, threads, smem, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, (int)(smem / 16), k, kb, g.nrows, nvec);
+        fn<<<grid, threads, smem, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, kpad, k, kb, g.nrows, nvec,
+                                       16u * g.width * 0x01010101u);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;

@@ -121,7 +121,7 @@ def test_encode_vs_oracle(rs, orc, torch, k, p, L):
     assert (got == want).all()
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4])  # default, PRMT splice, shift-mask, DP4A, mixed
 @pytest.mark.parametrize("k,p,L", [(10, 4, 200_000), (32, 8, 50_000), (11, 3, 40_001)])
 def test_encode_variants_vs_oracle(rs, orc, torch, variant, k, p, L):
     data = splitmix64_bytes(77 + variant, k * L).reshape(k, L)
