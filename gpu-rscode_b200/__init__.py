@@ -30,7 +30,7 @@ RSGPU_ETOOBIG = -6
 
 # every symbol include/rsgpu.h declares (tests check the library exports each of them)
 ABI_SYMBOLS = [
-    "rsgpu_strerror", "rsgpu_last_error", "rsgpu_device_count", "rsgpu_create", "rsgpu_create_with_matrix",
+    "rsgpu_strerror", "rsgpu_last_error", "rsgpu_device_count", "rsgpu_device_max_grid", "rsgpu_create", "rsgpu_create_with_matrix",
     "rsgpu_destroy", "rsgpu_k", "rsgpu_p", "rsgpu_device", "rsgpu_get_total_matrix", "rsgpu_encode",
     "rsgpu_set_survivors", "rsgpu_get_decode_matrix", "rsgpu_get_erased", "rsgpu_decode", "rsgpu_decode_erased",
     "rsgpu_invert_matrix", "rsgpu_matmul", "rsgpu_encode_host", "rsgpu_decode_host", "rsgpu_decode_erased_host", "rsgpu_host_alloc",
@@ -71,6 +71,7 @@ def lib():
     L.rsgpu_strerror.argtypes = [i32]
     L.rsgpu_last_error.restype = C.c_char_p
     L.rsgpu_device_count.argtypes = [C.POINTER(i32)]
+    L.rsgpu_device_max_grid.argtypes = [i32, C.POINTER(i32)]
     L.rsgpu_create.argtypes = [C.POINTER(vp), i32, i32, i32]
     L.rsgpu_create_with_matrix.argtypes = [C.POINTER(vp), i32, i32, i32, u8p]
     L.rsgpu_destroy.argtypes = [vp]

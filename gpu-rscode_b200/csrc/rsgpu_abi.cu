@@ -185,6 +185,16 @@ int rsgpu_device_count(int *count)
     return RSGPU_OK;
 }
 
+int rsgpu_device_max_grid(int device, int *max_grid)
+{
+    if (!max_grid) return fail_msg(RSGPU_EINVAL, "max_grid is NULL");
+    int gx = 0, gy = 0;
+    CK(cudaDeviceGetAttribute(&gx, cudaDevAttrMaxGridDimX, device));
+    CK(cudaDeviceGetAttribute(&gy, cudaDevAttrMaxGridDimY, device));
+    *max_grid = gx < gy ? gx : gy;
+    return RSGPU_OK;
+}
+
 int rsgpu_create(rsgpu_ctx **out, int device, int k, int p) { return ctx_create(out, device, k, p, nullptr); }
 
 int rsgpu_create_with_matrix(rsgpu_ctx **out, int device, int k, int p, const uint8_t *total_matrix)

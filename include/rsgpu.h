@@ -43,6 +43,10 @@ const char *rsgpu_last_error(void);
 /* Number of visible CUDA devices.  Replaces cudaGetDeviceCount in src/encode.cu:357, decode.cu:335. */
 int rsgpu_device_count(int *count);
 
+/* Largest legal gridDim.x/y of `device` -- the bound the reference prints as "Valid grid size: (0, %d]"
+ * (min of maxGridSize[0], maxGridSize[1], src/encode.cu:348-355). */
+int rsgpu_device_max_grid(int device, int *max_grid);
+
 /*
  * Create a coding context for RS(k, k+p) on `device`.
  * Builds on the GPU: the GF(2^8) exp/log tables (replaces setup_tables, src/matrix.cu:47-75), the

@@ -40,3 +40,14 @@ def test_no_cpu_fallback_without_gpu():
     with pytest.raises(rs.RSGPUError) as ei:
         rs.RSContext(4, 2)
     assert ei.value.code == rs.RSGPU_ECUDA
+
+
+def test_host_library_exports_reference_entry_points():
+    """include/encode.h / decode.h: the C host layer exports the reference's two symbols (C linkage)."""
+    import ctypes
+    if not os.path.exists(rs.HOST_LIB_PATH):
+        rs.build()
+    ctypes.CDLL(rs.LIB_PATH, mode=ctypes.RTLD_GLOBAL)
+    H = ctypes.CDLL(rs.HOST_LIB_PATH)
+    assert hasattr(H, "encode_file") and hasattr(H, "decode_file")
+    assert os.access(rs.RS_BIN, os.X_OK)
