@@ -2,8 +2,10 @@
  *   encode:  RS -k K -n N -e file            [-p maxGridDimX] [-s streams]
  *   decode:  RS -d -i file -c conf [-o out]  [-p maxGridDimX] [-s streams]
  * -d must come before -i/-c/-o (otherwise the usage text is shown, src/main.c:104-137); decoding
- * takes k and n from the METADATA file.  One deliberate difference: without -s the stream count is
- * chosen by the engine (the reference defaults to 1, which never overlaps copies and kernels).
+ * takes k and n from the METADATA file.  Two deliberate differences: without -s the stream count is
+ * chosen by the engine (the reference defaults to 1, which never overlaps copies and kernels); and the
+ * documented upper-case spellings -K -N -E -I -C -O -S -P take their argument here -- the reference's
+ * getopt string "Ss:Pp:Kk:..." gives them none, so it dereferences a NULL optarg and crashes.
  */
 #include <assert.h>
 #include <getopt.h>
@@ -34,7 +36,7 @@ int main(int argc, char *argv[])
     char *inFile = NULL, *confFile = NULL, *outFile = NULL;
     enum { NONE, ENCODE, DECODE } op = NONE;
     int option;
-    while ((option = getopt(argc, argv, "Ss:Pp:Kk:Nn:Ee:Ii:Cc:Oo:Ddh")) != -1) {
+    while ((option = getopt(argc, argv, "S:s:P:p:K:k:N:n:E:e:I:i:C:c:O:o:Ddh")) != -1) {
         switch (option) {
         case 'S': case 's': streams = atoi(optarg); break;
         case 'P': case 'p': grid = atoi(optarg); break;
