@@ -36,6 +36,7 @@ ABI_SYMBOLS = [
     "rsgpu_invert_matrix", "rsgpu_matmul", "rsgpu_encode_host", "rsgpu_decode_host", "rsgpu_decode_erased_host", "rsgpu_host_alloc",
     "rsgpu_host_free", "rsgpu_host_register", "rsgpu_host_unregister", "rsgpu_dev_alloc", "rsgpu_dev_free",
     "rsgpu_memcpy_h2d", "rsgpu_memcpy_d2h", "rsgpu_sync", "rsgpu_set_tuning", "rsgpu_launch_count",
+    "rsgpu_encode_noalloc",
 ]
 
 
@@ -102,6 +103,7 @@ def lib():
     L.rsgpu_set_tuning.argtypes = [vp, i32, i32, i32]
     L.rsgpu_launch_count.argtypes = [vp]
     L.rsgpu_launch_count.restype = C.c_longlong
+    L.rsgpu_encode_noalloc.argtypes = [i32, i32, u8p, sz, u8p, sz, sz, vp]
     _lib = L
     return L
 
@@ -250,6 +252,11 @@ class RSContext:
 
     def d2h(self, dst: np.ndarray, src_d):
         _check(lib().rsgpu_memcpy_d2h(self._h, dst.ctypes.data, src_d, dst.nbytes))
+
+
+def encode_noalloc(k, p, data_d, data_pitch, parity_d, parity_pitch, length, stream=0):
+    """rsgpu_encode_noalloc on the current CUDA device: no context, no allocation (k <= 32, p <= 8)."""
+    _check(lib().rsgpu_encode_noalloc(k, p, _ptr(data_d), data_pitch, _ptr(parity_d), parity_pitch, length, stream))
 
 
 def host_alloc(nbytes):

@@ -162,6 +162,34 @@ int rsgpu_memcpy_d2h(rsgpu_ctx *ctx, void *dst, const void *src_d, size_t bytes)
 int rsgpu_sync(rsgpu_ctx *ctx);
 
 /*
+ * Encode without allocating anything (no counterpart in the reference, which cudaMallocs on every
+ * call, src/encode.cu:168-190).
+ *
+ * For callers that are not allowed to allocate GPU memory once they are running: engines embedded in
+ * a process whose device memory was handed out as fixed arenas at start-up, or sitting in an I/O path
+ * where the device-wide serialisation of cudaMalloc/cudaFree would stall every other stream.  Those
+ * callers cannot use rsgpu_create.  This call needs no context: the GF tables, the generator matrix
+ * [I;V] and the product tables are rebuilt on `stream` into a fixed 16 KiB array that is part of the
+ * library image (each GPU that loads librsgpu.so holds it until the process exits), then the same
+ * multiply kernel as rsgpu_encode runs.  Same arguments and result bytes as rsgpu_encode; works on the
+ * CURRENT device; inputs and outputs are still the caller's buffers.
+ *
+ * Limits and rules:
+ *   - k <= RSGPU_NOALLOC_MAX_K (32) and 1 <= p <= RSGPU_NOALLOC_MAX_P (8); anything larger returns
+ *     RSGPU_ETOOBIG and does nothing.
+ *   - The first call on each device looks up the array's device address (a one-time host-side query,
+ *     made with that device current).  Make that first call before you start capturing a stream.
+ *   - All calls on a device share the one array and each call rewrites it: two calls whose GPU work
+ *     can overlap (different streams, or different host threads) race on it.  Issue them on one
+ *     stream, or otherwise order them.
+ *   - It performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ */
+#define RSGPU_NOALLOC_MAX_K 32
+#define RSGPU_NOALLOC_MAX_P 8
+int rsgpu_encode_noalloc(int k, int p, const uint8_t *data_d, size_t data_pitch,
+                         uint8_t *parity_d, size_t parity_pitch, size_t len, void *stream);
+
+/*
  * Tuning knobs of the multiply kernel (the reference's -p grid cap, src/main.c:75-78, maps to
  * max_blocks).  variant: 0 = default, see DESIGN.md for the list; threads: block size (0 = default);
  * max_blocks: cap on gridDim.x (0 = persistent grid sized from the SM count).
