@@ -229,6 +229,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (the product path has no CPU fallback)")
     rs = importlib.import_module("gpu-rscode_b200")
+    sharding = importlib.import_module("gpu-rscode_b200.sharding")
     rs.lib()
 
     torch.cuda.set_device(local_rank)
@@ -311,7 +312,7 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     elapsed_ms = float(t.item())
-    value = n_gpus * k * L * args.steps / (elapsed_ms / 1e3) / 1e9
+    value = sharding.job_throughput_gbs(k * L, n_gpus, args.steps, elapsed_ms)
 
     # ---- correctness spot check of what was just timed (oracle on a 64 KiB window) ----
     check = "skipped"

@@ -53,5 +53,7 @@ typedef struct {
 } rs_job;
 
 int rs_run_job(rs_job *job); /* returns job->error */
+int rs_plan_gpus(size_t len, int visible);
+void rs_partition(size_t len, int parts, int g, size_t *off, size_t *n);
 
 #endif

@@ -92,6 +92,27 @@ static void *worker_main(void *arg)
     return NULL;
 }
 
+/* How many of the `visible` GPUs a stripe of `len` bytes per fragment is spread over: a GPU is worth
+ * starting only for a few MiB, tiny inputs stay on GPU 0. */
+int rs_plan_gpus(size_t len, int visible)
+{
+    const size_t min_range = (size_t)4 << 20;
+    int use = visible < 1 ? 1 : visible;
+    while (use > 1 && len / (size_t)use < min_range)
+        --use;
+    return use;
+}
+
+/* Byte range [*off, *off + *n) of every fragment that GPU g of `parts` owns: contiguous, boundaries on
+ * 256 bytes so every GPU keeps 16-byte aligned rows, the last GPU takes the remainder (the reference
+ * splits the same way without the alignment, src/encode.cu:368-381). */
+void rs_partition(size_t len, int parts, int g, size_t *off, size_t *n)
+{
+    const size_t per = (len / (size_t)parts) / 256 * 256;
+    *off = (size_t)g * per;
+    *n = (g == parts - 1) ? len - *off : per;
+}
+
 int rs_run_job(rs_job *job)
 {
     job->error = 0;
@@ -104,26 +125,18 @@ int rs_run_job(rs_job *job)
         snprintf(job->error_text, sizeof job->error_text, "no usable CUDA device: %s", rsgpu_last_error());
         return job->error;
     }
-    /* a GPU is worth starting only for a few MiB; tiny inputs stay on GPU 0 */
-    const size_t min_range = (size_t)4 << 20;
-    int use = n;
-    while (use > 1 && job->len / (size_t)use < min_range)
-        --use;
+    const int use = rs_plan_gpus(job->len, n);
     job->n_gpus = use;
 
     worker_t *w = calloc((size_t)use, sizeof *w);
     pthread_t *th = calloc((size_t)use, sizeof *th);
     pthread_barrier_t barrier;
     pthread_barrier_init(&barrier, NULL, (unsigned)use);
-    /* contiguous byte ranges, boundaries on 256 bytes so every GPU keeps 16-byte aligned rows;
-     * the last GPU takes the remainder (reference: src/encode.cu:368-381) */
-    const size_t per = (job->len / (size_t)use) / 256 * 256;
     for (int g = 0; g < use; ++g) {
         w[g].job = job;
         w[g].gpu = g;
         w[g].barrier = &barrier;
-        w[g].off = (size_t)g * per;
-        w[g].len = (g == use - 1) ? job->len - w[g].off : per;
+        rs_partition(job->len, use, g, &w[g].off, &w[g].len);
         pthread_create(&th[g], NULL, worker_main, &w[g]);
     }
     for (int g = 0; g < use; ++g)
