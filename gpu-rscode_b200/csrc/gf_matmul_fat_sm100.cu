@@ -1,0 +1,390 @@
+// gf_matmul_fat_sm100.cu -- second generation of the hot kernel: bank-replicated byte tables.
+//
+// Why: the split-nibble kernel (gf_matmul_sm100.cu) is bound by the shared-memory data pipe, not by
+// HBM: every input byte costs two 4-byte lookups = two wavefronts per warp, and at 1 wavefront per clock
+// per SM that caps a B200 at ~4.1 TB/s of input, below the ~4.6 TB/s that HBM allows for RS(10,14)
+// (profiles/r1_*: lsu pipe 82 %, shared wavefronts 78 % + global 17 %, zero bank conflicts).
+// The only way down is ONE lookup per input byte.  A 256-entry table indexed by the whole byte would
+// bank-conflict ~3.5-way on random data -- unless every lane owns its bank: the table is stored
+// [x][lane], 32 replicas of each 4-byte entry side by side (16 replicas of 8-byte entries for the
+// 64-bit width), so lane l always reads bank l whatever x is.  That costs 32 KiB of shared memory per
+// input fragment ("fat8"), or 16 KiB if bit 7 of the byte is peeled off and handled in registers
+// ("fat7": index = low 7 bits, plus (sign mask & product-of-0x80) from one PRMT and one LOP3).
+// With 227 KiB per SM a block holds e.g. 4 fat8 + 6 fat7 tables for k = 10, or 14 fat7 + 2 nibble pages
+// for k = 16; fragments that do not fit keep the split-nibble tables.  One block of 512-768 threads per
+// SM builds the replicated tables once (from the same 32-entry global tables the other kernel uses) and
+// then streams columns exactly like the first kernel: 128-bit loads, register double buffering, XOR
+// accumulate, PRMT transpose, 128-bit stores.
+//
+// Index arithmetic: address = lane_base + x * 128.  __dp4a(w, 0x80 << 8b, lane_base) selects byte b of
+// the data word, scales it by 128 and adds the lane base in ONE fmaheavy-pipe instruction, no mask, no
+// shift (fat7 masks the word with 0x7F7F7F7F once per four bytes).  The per-fragment table offset is a
+// compile-time immediate of the LDS.
+#include <stdlib.h>
+
+#include "rs_internal.h"
+
+namespace rsgpu {
+namespace {
+
+constexpr int kSmemBudget = 232448 - 512;   // 227 KiB opt-in limit minus alignment slack
+
+__host__ __device__ constexpr int fat_count(int k)
+{
+    // every fragment wants at least a fat7 table (16 KiB); thin pages (256 B) for the rest
+    int n = k;
+    while (n > 0 && n * 16384 + (k - n) * 256 > kSmemBudget) --n;
+    return n;
+}
+__host__ __device__ constexpr int fat8_count(int k)
+{
+    const int n = fat_count(k);
+    int left = kSmemBudget - n * 16384 - (k - n) * 256;
+    int n8 = left / 16384;
+    return n8 > n ? n : n8;
+}
+__host__ __device__ constexpr int fat_smem_bytes(int k)
+{
+    return fat_count(k) * 16384 + fat8_count(k) * 16384 + (k - fat_count(k)) * 256;
+}
+__host__ __device__ constexpr int fat_threads(int W, int JB)
+{
+    // register budget: accumulators (16 or 32) + two batches of JB vectors
+    if (W == 4) return JB <= 2 ? 1024 : (JB <= 4 ? 768 : (JB <= 5 ? 640 : 512));
+    return JB <= 2 ? 768 : (JB <= 5 ? 512 : 384);
+}
+
+__device__ __forceinline__ uint4 ldg_stream(const uint8_t *p)
+{
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void stg_stream(uint8_t *p, uint4 v)
+{
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <int OFF> __device__ __forceinline__ uint32_t lds32(uint32_t addr)
+{
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF));
+    return v;
+}
+template <int OFF> __device__ __forceinline__ uint2 lds64(uint32_t addr)
+{
+    uint2 v;
+    asm("ld.shared.v2.u32 {%0,%1}, [%2+%3];" : "=r"(v.x), "=r"(v.y) : "r"(addr), "n"(OFF));
+    return v;
+}
+// volatile: keeps the per-fragment constant load next to its use instead of hoisting one register per
+// fragment out of the column loop
+template <int OFF> __device__ __forceinline__ uint32_t lds32_pinned(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF));
+    return v;
+}
+
+template <int W> struct Acc;
+template <> struct Acc<4> { uint32_t a[16]; };
+template <> struct Acc<8> { uint32_t a[16]; uint32_t b[16]; };
+
+// Shared-memory map for a K-fragment code (all offsets relative to the 256-aligned base tb):
+//   fragments [0, N8)        fat8 tables, 32 KiB each
+//   fragments [N8, NF)       fat7 tables, 16 KiB each
+//   fragments [NF, K)        split-nibble pages, 256 B each
+//   then K * 8 bytes: the product of 0x80 with every coefficient (bit-7 term of the fat7 fragments)
+template <int K> struct Map {
+    static constexpr int NF = fat_count(K);
+    static constexpr int N8 = fat8_count(K);
+    static constexpr int THIN0 = N8 * 32768 + (NF - N8) * 16384;
+    static constexpr int C7 = THIN0 + (K - NF) * 256;
+    static constexpr int BYTES = C7 + K * 8;
+    __host__ __device__ static constexpr int off(int j)
+    {
+        return j < N8 ? j * 32768 : (j < NF ? N8 * 32768 + (j - N8) * 16384 : THIN0 + (j - NF) * 256);
+    }
+};
+
+template <int W, int K, int J>
+__device__ __forceinline__ void mac_word(uint32_t w, uint32_t lane_base, uint32_t tb, uint32_t c7a, uint32_t c7b,
+                                         Acc<W> &acc, int pos0)
+{
+    using M = Map<K>;
+    constexpr int OFF = M::off(J);
+    if constexpr (J < M::NF) {
+        constexpr bool F7 = (J >= M::N8);
+        const uint32_t wi = F7 ? (w & 0x7F7F7F7Fu) : w;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const uint32_t addr = __dp4a(wi, 0x80u << (8 * b), lane_base);
+            uint32_t va, vb = 0;
+            if constexpr (W == 4) {
+                va = lds32<OFF>(addr);
+            } else {
+                const uint2 v = lds64<OFF>(addr);
+                va = v.x;
+                vb = v.y;
+            }
+            if constexpr (F7) {
+                // PRMT with the sign-replicate flag (selector nibble 8|b): 0xFFFFFFFF if bit 7 of byte b
+                // is set, else 0.  Raw PTX: the __byte_perm intrinsic drops bit 3 of the selector nibbles.
+                uint32_t m;
+                asm("prmt.b32 %0, %1, %2, %3;" : "=r"(m) : "r"(w), "r"(0u), "r"(0x8888u + 0x1111u * b));
+                va ^= m & c7a;
+                if constexpr (W == 8) vb ^= m & c7b;
+            }
+            acc.a[pos0 + b] ^= va;
+            if constexpr (W == 8) acc.b[pos0 + b] ^= vb;
+        }
+    } else {
+        // split-nibble page (same scheme as gf_matmul_sm100.cu, DP4A extraction)
+        constexpr int SH = (W == 4) ? 2 : 3;
+        constexpr uint32_t M4 = (0xFu << SH) * 0x01010101u;
+        const uint32_t wl = (w << SH) & M4;
+        const uint32_t wh = (w >> (4 - SH)) & M4;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const uint32_t alo = __dp4a(wl, 1u << (8 * b), tb);
+            const uint32_t ahi = __dp4a(wh, 1u << (8 * b), tb);
+            if constexpr (W == 4) {
+                acc.a[pos0 + b] ^= lds32<OFF>(alo) ^ lds32<OFF + 16 * W>(ahi);
+            } else {
+                const uint2 l = lds64<OFF>(alo), h = lds64<OFF + 16 * W>(ahi);
+                acc.a[pos0 + b] ^= l.x ^ h.x;
+                acc.b[pos0 + b] ^= l.y ^ h.y;
+            }
+        }
+    }
+}
+
+template <int W, int K, int J>
+__device__ __forceinline__ void mac_vec(const uint4 &d, uint32_t lane_base, uint32_t tb, Acc<W> &acc)
+{
+    using M = Map<K>;
+    uint32_t c7a = 0, c7b = 0;
+    if constexpr (J >= M::N8 && J < M::NF) {   // fat7: the bit-7 term, one broadcast load per 16 bytes
+        c7a = lds32_pinned<M::C7 + J * 8>(tb);
+        if constexpr (W == 8) c7b = lds32_pinned<M::C7 + J * 8 + 4>(tb);
+    }
+    mac_word<W, K, J>(d.x, lane_base, tb, c7a, c7b, acc, 0);
+    mac_word<W, K, J>(d.y, lane_base, tb, c7a, c7b, acc, 4);
+    mac_word<W, K, J>(d.z, lane_base, tb, c7a, c7b, acc, 8);
+    mac_word<W, K, J>(d.w, lane_base, tb, c7a, c7b, acc, 12);
+}
+
+// compile-time loop over the fragments of batch B
+template <int W, int K, int JB, int B, int JJ>
+struct BatchMac {
+    __device__ __forceinline__ static void run(const uint4 (&d)[JB], uint32_t lane_base, uint32_t tb, Acc<W> &acc)
+    {
+        mac_vec<W, K, B * JB + JJ>(d[JJ], lane_base, tb, acc);
+        if constexpr (JJ + 1 < JB) BatchMac<W, K, JB, B, JJ + 1>::run(d, lane_base, tb, acc);
+    }
+};
+
+__device__ __forceinline__ void transpose_store(const uint32_t *a, uint8_t *out, size_t out_pitch, size_t off,
+                                                int row0, int nrows)
+{
+    uint32_t r[4][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint32_t a0 = a[4 * q], a1 = a[4 * q + 1], a2 = a[4 * q + 2], a3 = a[4 * q + 3];
+        const uint32_t t0 = __byte_perm(a0, a1, 0x5140), t1 = __byte_perm(a2, a3, 0x5140);
+        const uint32_t t2 = __byte_perm(a0, a1, 0x7362), t3 = __byte_perm(a2, a3, 0x7362);
+        r[0][q] = __byte_perm(t0, t1, 0x5410);
+        r[1][q] = __byte_perm(t0, t1, 0x7632);
+        r[2][q] = __byte_perm(t2, t3, 0x5410);
+        r[3][q] = __byte_perm(t2, t3, 0x7632);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        if (i < nrows)
+            stg_stream(out + (size_t)(row0 + i) * out_pitch + off, make_uint4(r[i][0], r[i][1], r[i][2], r[i][3]));
+}
+
+template <int JB>
+__device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *&q, size_t in_pitch)
+{
+#pragma unroll
+    for (int jj = 0; jj < JB; ++jj) {
+        d[jj] = ldg_stream(q);
+        q += in_pitch;
+    }
+}
+
+// One column = KB batches, all compile time (every LDS offset is an immediate).  The two register
+// buffers alternate per batch ("ping-pong"): the loads of batch t+1 go into the buffer batch t-1 has just
+// released and are issued BEFORE batch t is consumed, so they have a whole batch of work to land and no
+// register-to-register copies are needed.  SP = which buffer holds batch 0 of this column.
+template <int W, int K, int JB, int KB, int B, int SP>
+struct ColumnBatches {
+    __device__ __forceinline__ static void run(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
+                                               const uint8_t *in, size_t vn, size_t nvec, uint32_t lane_base,
+                                               uint32_t tb, Acc<W> &acc)
+    {
+        constexpr int PAR = (SP + B) & 1;
+        uint4 (&cur)[JB] = PAR ? buf1 : buf0;
+        uint4 (&nxt)[JB] = PAR ? buf0 : buf1;
+        if constexpr (B + 1 < KB) {
+            load_batch<JB>(nxt, q, in_pitch);
+        } else {
+            if (vn < nvec) {
+                q = in + vn * 16;
+                load_batch<JB>(nxt, q, in_pitch);
+            }
+        }
+        BatchMac<W, K, JB, B, 0>::run(cur, lane_base, tb, acc);
+        if constexpr (B + 1 < KB)
+            ColumnBatches<W, K, JB, KB, B + 1, SP>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc);
+    }
+};
+
+template <int W, int K, int JB, int KB, int SP>
+__device__ __forceinline__ void do_column(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
+                                          const uint8_t *in, uint8_t *out, size_t out_pitch, size_t v, size_t vn,
+                                          size_t nvec, uint32_t lane_base, uint32_t tb, int nrows)
+{
+    Acc<W> acc;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        acc.a[i] = 0;
+        if constexpr (W == 8) acc.b[i] = 0;
+    }
+    ColumnBatches<W, K, JB, KB, 0, SP>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc);
+    transpose_store(acc.a, out, out_pitch, v * 16, 0, nrows);
+    if constexpr (W == 8) transpose_store(acc.b, out, out_pitch, v * 16, 4, nrows - 4);
+}
+
+template <int W, int JB, int KB>
+__global__ void __launch_bounds__(fat_threads(W, JB), 1)
+k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
+                const uint32_t *__restrict__ tab, int nrows, size_t nvec)
+{
+    constexpr int K = JB * KB;
+    using M = Map<K>;
+    constexpr int WW = W / 4;            // words per entry
+    constexpr int REP = 128 / W;         // replicas per entry: 32 (W=4) or 16 (W=8); one 128-byte row per x
+    extern __shared__ __align__(16) uint8_t s_raw[];
+    const uint32_t tb = ((uint32_t)__cvta_generic_to_shared(s_raw) + 255u) & ~255u;
+    const int tid = threadIdx.x, nt = blockDim.x;
+
+    // ---- build the tables of this block from the 32-entry global tables (lo 16 + hi 16 per fragment) ----
+    for (int j = 0; j < M::NF; ++j) {
+        const int nx = j < M::N8 ? 256 : 128;
+        const uint32_t base = tb + M::off(j);
+        const uint32_t *tj = tab + (size_t)j * 32 * WW;
+        for (int i = tid; i < nx * REP; i += nt) {
+            const int x = i / REP, r = i - x * REP;
+#pragma unroll
+            for (int q = 0; q < WW; ++q) {
+                const uint32_t v = __ldg(tj + (x & 15) * WW + q) ^ __ldg(tj + (16 + (x >> 4)) * WW + q);
+                asm volatile("st.shared.u32 [%0], %1;" ::"r"(base + x * 128 + r * W + q * 4), "r"(v) : "memory");
+            }
+        }
+    }
+    for (int i = tid; i < (K - M::NF) * 32 * WW; i += nt) {   // thin pages: straight copy, 256-byte stride
+        const int j = i / (32 * WW), r = i - j * (32 * WW);
+        const uint32_t v = __ldg(tab + (size_t)(M::NF + j) * 32 * WW + r);
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(tb + M::THIN0 + j * 256 + r * 4), "r"(v) : "memory");
+    }
+    for (int i = tid; i < K * 2; i += nt) {                   // product of 0x80 = hi-table entry 8
+        const int j = i >> 1, q = i & 1;
+        const uint32_t v = q < WW ? __ldg(tab + (size_t)j * 32 * WW + (16 + 8) * WW + q) : 0u;
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(tb + M::C7 + i * 4), "r"(v) : "memory");
+    }
+    __syncthreads();
+
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lane_base = tb + (W == 4 ? lane * 4u : (lane & 15u) * 8u);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint4 buf0[JB], buf1[JB];
+    const uint8_t *q = in + v * 16;
+    if (v < nvec) load_batch<JB>(buf0, q, in_pitch);
+
+    while (v < nvec) {
+        do_column<W, K, JB, KB, 0>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows);
+        v += stride;
+        if constexpr (KB & 1) {          // odd batch count: the next column starts in the other buffer
+            if (v >= nvec) break;
+            do_column<W, K, JB, KB, 1>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows);
+            v += stride;
+        }
+    }
+}
+
+using FatFn = void (*)(const uint8_t *, size_t, uint8_t *, size_t, const uint32_t *, int, size_t);
+
+struct FatKernel {
+    FatFn fn;
+    int threads;
+    int smem;
+};
+
+template <int W, int JB, int KB>
+FatKernel make_fat()
+{
+    return FatKernel{k_gf_matmul_fat<W, JB, KB>, fat_threads(W, JB), Map<JB * KB>::BYTES + 256};
+}
+
+template <int W>
+bool pick_fat_alt(int k, FatKernel *fk)   // developer experiment (RSGPU_FAT_ALT): other batch shapes
+{
+    switch (k) {
+    case 10: *fk = make_fat<W, 5, 2>(); return true;
+    case 14: *fk = make_fat<W, 2, 7>(); return true;
+    case 20: *fk = make_fat<W, 4, 5>(); return true;
+    default: return false;
+    }
+}
+
+// Batch shape per k (JB fragments per batch x KB batches), measured on B200: batches of 4 with 768
+// threads beat batches of 8 with 512 (RS(16,20): 0.888 vs 0.794 of the HBM peak, RS(8,12): 0.898 vs 0.816);
+// RS(10,14): batches of 2 with 1024 threads 0.900, batches of 5 with 640 threads 0.869.
+template <int W>
+bool pick_fat(int k, FatKernel *fk)
+{
+    static const bool alt = getenv("RSGPU_FAT_ALT") != nullptr;
+    if (alt && pick_fat_alt<W>(k, fk)) return true;
+    switch (k) {
+    case 4: *fk = make_fat<W, 4, 1>(); return true;
+    case 6: *fk = make_fat<W, 6, 1>(); return true;
+    case 8: *fk = make_fat<W, 4, 2>(); return true;
+    case 10: *fk = make_fat<W, 2, 5>(); return true;
+    case 12: *fk = make_fat<W, 4, 3>(); return true;
+    case 14: *fk = make_fat<W, 7, 2>(); return true;
+    case 16: *fk = make_fat<W, 4, 4>(); return true;
+    case 20: *fk = make_fat<W, 5, 4>(); return true;
+    case 24: *fk = make_fat<W, 4, 6>(); return true;
+    case 32: *fk = make_fat<W, 4, 8>(); return true;
+    default: return false;
+    }
+}
+
+}  // namespace
+
+// Returns cudaErrorNotSupported when no bank-replicated instance exists for this k (the caller then
+// uses the split-nibble kernel).  Vector part only: nvec 16-byte columns.
+cudaError_t launch_matmul_fat(const RowGroup &g, int k, const uint8_t *in, size_t in_pitch, uint8_t *out_g,
+                              size_t out_pitch, size_t nvec, const DeviceInfo &dev, int max_blocks, int threads,
+                              cudaStream_t s)
+{
+    FatKernel fk;
+    const bool ok = g.width == 4 ? pick_fat<4>(k, &fk) : pick_fat<8>(k, &fk);
+    if (!ok || fk.smem > dev.max_smem_optin) return cudaErrorNotSupported;
+    if (threads > 0 && threads < fk.threads) fk.threads = threads;   // tuning: fewer threads than the launch bound
+    cudaError_t e = cudaFuncSetAttribute((const void *)fk.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, fk.smem);
+    if (e != cudaSuccess) return e;
+    size_t want = (nvec + fk.threads - 1) / fk.threads;
+    size_t cap = (size_t)dev.sm_count;      // one block per SM: the tables fill its shared memory
+    if (max_blocks > 0 && (size_t)max_blocks < cap) cap = max_blocks;
+    const unsigned grid = (unsigned)(want < cap ? want : cap);
+    fk.fn<<<grid, fk.threads, fk.smem, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, g.nrows, nvec);
+    return cudaGetLastError();
+}
+
+}  // namespace rsgpu

@@ -313,14 +313,27 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
     uint8_t *out_g = out + (size_t)g.row0 * out_pitch;
     const bool aligned = (((uintptr_t)in | (uintptr_t)out_g | in_pitch | out_pitch) & 15u) == 0;
     const size_t nvec = aligned ? len / 16 : 0;
-    const int threads = tune.threads > 0 ? tune.threads : 256;
+    const int threads = (tune.threads > 0 && tune.threads <= 256) ? tune.threads : 256;
 
-    if (nvec) {
+    // variant 0 (default): the bank-replicated kernel when an instance exists for this k and the stripe
+    // is long enough to pay for building its tables (one 227 KiB fill per SM, ~8 us: measured break-even
+    // on B200 at 16 MiB per fragment for RS(10,14)); 5 forces it, 6 forbids it
+    bool done_vec = false;
+    if (nvec && (tune.variant == 5 || (tune.variant == 0 && len >= ((size_t)12 << 20)))) {
+        cudaError_t e = launch_matmul_fat(g, k, in, in_pitch, out_g, out_pitch, nvec, dev, tune.max_blocks, tune.threads, s);
+        if (e == cudaSuccess) {
+            done_vec = true;
+            if (launches) ++*launches;
+        } else if (e != cudaErrorNotSupported) {
+            return e;
+        }
+    }
+    if (nvec && !done_vec) {
         const int jb = choose_jb(k);
         const int kb = (k + jb - 1) / jb;           // kb*jb <= kpad because kpad is k rounded up to 8
         // variant 0 = default = DP4A extraction (EX 2): same speed as the PRMT splice on B200 but it
         // leaves the alu pipe at 45% instead of 81% (ncu, profiles/r1_pipes.md); 1..4 select EX 0..3
-        const int ex = tune.variant == 0 ? 2 : (tune.variant - 1) % 4;
+        const int ex = (tune.variant == 0 || tune.variant > 4) ? 2 : (tune.variant - 1) % 4;
         MatmulFn fn = pick_kernel(g.width, jb, ex, kb * jb > k);
         const size_t smem = (size_t)kpad * 256 + 256;   // one page per fragment + alignment slack
         if (smem > 48 * 1024) {

@@ -73,4 +73,12 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
                                 size_t len, const Tuning &tune, const DeviceInfo &dev,
                                 cudaStream_t s, long long *launches);
 
+
+// ---- gf_matmul_fat_sm100.cu -------------------------------------------------------------------
+// Bank-replicated byte-table kernel (one lookup per input byte).  cudaErrorNotSupported = no instance
+// for this k: use the split-nibble kernel.  Handles the nvec 16-byte columns only.
+cudaError_t launch_matmul_fat(const RowGroup &g, int k, const uint8_t *in, size_t in_pitch, uint8_t *out_g,
+                              size_t out_pitch, size_t nvec, const DeviceInfo &dev, int max_blocks, int threads,
+                              cudaStream_t s);
+
 }  // namespace rsgpu

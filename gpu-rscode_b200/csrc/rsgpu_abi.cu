@@ -452,7 +452,7 @@ int rsgpu_sync(rsgpu_ctx *c)
 int rsgpu_set_tuning(rsgpu_ctx *c, int variant, int threads, int max_blocks)
 {
     if (!c) return fail_msg(RSGPU_EINVAL, "NULL argument");
-    if (threads < 0 || threads > 256 || (threads % 32) != 0) return fail_msg(RSGPU_EINVAL, "threads must be a multiple of 32, <= 256");
+    if (threads < 0 || threads > 1024 || (threads % 32) != 0) return fail_msg(RSGPU_EINVAL, "threads must be a multiple of 32, <= 1024");
     if (variant < 0 || max_blocks < 0) return fail_msg(RSGPU_EINVAL, "negative tuning value");
     c->tune.variant = variant;
     c->tune.threads = threads;

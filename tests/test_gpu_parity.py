@@ -121,7 +121,7 @@ def test_encode_vs_oracle(rs, orc, torch, k, p, L):
     assert (got == want).all()
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4])  # default, PRMT splice, shift-mask, DP4A, mixed
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6])  # auto, PRMT splice, shift-mask, DP4A, mixed, byte tables, nibble only
 @pytest.mark.parametrize("k,p,L", [(10, 4, 200_000), (32, 8, 50_000), (11, 3, 40_001)])
 def test_encode_variants_vs_oracle(rs, orc, torch, variant, k, p, L):
     data = splitmix64_bytes(77 + variant, k * L).reshape(k, L)
@@ -129,6 +129,22 @@ def test_encode_variants_vs_oracle(rs, orc, torch, variant, k, p, L):
         ctx.set_tuning(variant=variant)
         got = gpu_encode(torch, ctx, data)
     assert (got == orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)).all()
+
+
+@pytest.mark.parametrize("k", [4, 6, 8, 10, 12, 14, 16, 20, 24, 32])
+@pytest.mark.parametrize("p", [1, 4, 5, 8])
+def test_encode_bank_replicated_kernel_vs_oracle(rs, orc, torch, k, p):
+    """variant 5 forces the byte-table kernel (fat8 / fat7 / nibble mix depends on k) at a small size."""
+    L = 150_000 + 16 * k + 3
+    data = splitmix64_bytes(500 + k * 7 + p, k * L).reshape(k, L)
+    data[:, :512] = np.arange(512, dtype=np.uint8)[None, :]          # every byte value, bit 7 included
+    with rs.RSContext(k, p) as ctx:
+        ctx.set_tuning(variant=5)
+        pitch = (L + 255) // 256 * 256                                # 16-byte aligned rows: the vector kernel runs
+        got = gpu_encode(torch, ctx, data, pitch=pitch, out_pitch=pitch)
+        n_launch = ctx.launch_count()
+    assert (got == orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)).all()
+    assert n_launch > 0
 
 
 def test_encode_pitch_and_misalignment(rs, orc, torch):

@@ -20,8 +20,8 @@ def main():
     ap.add_argument("--k", type=int, default=10)
     ap.add_argument("--p", type=int, default=4)
     ap.add_argument("--frag-mib", type=float, default=400)
-    ap.add_argument("--variants", default="0,1,2,3,4")
-    ap.add_argument("--threads", default="256")
+    ap.add_argument("--variants", default="0,5,6")
+    ap.add_argument("--threads", default="0")
     ap.add_argument("--blocks", default="0")
     ap.add_argument("--reps", type=int, default=20)
     args = ap.parse_args()
