@@ -30,30 +30,44 @@ typedef struct {
 int rs_read_conf(const char *path, int k, rs_conf *conf); /* 0 ok, -1 cannot open, -2 too few names */
 void rs_free_conf(rs_conf *conf);
 
-/* ---- sched.c : stripe scheduling over the visible GPUs ---- */
-typedef enum { RS_JOB_ENCODE, RS_JOB_DECODE_ERASED } rs_job_kind;
-
-typedef struct {
-    rs_job_kind kind;
-    int k, p;
-    const uint8_t *total_matrix; /* NULL: generate [I;V] on the GPU */
-    const int *survivors;        /* decode: k fragment indices in conf order */
-    const uint8_t *in;           /* [in_rows][pitch] host (pinned) */
-    uint8_t *out;                /* [out_rows][pitch] host (pinned) */
-    size_t in_pitch, out_pitch;
-    size_t len;                  /* bytes per fragment row */
-    int grid_cap;                /* reference -p, 0 = default */
-    int slots;                   /* reference -s, <= 0 = default */
-    /* results */
-    uint8_t *matrix_out;         /* if not NULL: receives GPU 0's (k+p) x k total matrix */
-    double wall_ms;              /* between the two barriers, as the reference measures it */
-    int n_gpus;
-    int error;                   /* first RSGPU_E* code seen by any worker, 0 if none */
-    char error_text[512];
-} rs_job;
-
-int rs_run_job(rs_job *job); /* returns job->error */
+/* ---- sched.c : how a stripe is spread over the visible GPUs ---- */
 int rs_plan_gpus(size_t len, int visible);
 void rs_partition(size_t len, int parts, int g, size_t *off, size_t *n);
+
+/* ---- stream.c : streaming slab pipeline  file -> pinned ring -> GPU(s) -> files ---- */
+typedef struct {
+    int fd;          /* input row r of a slab = pread(fd, base + column offset) ; short reads give zeros */
+    long long base;
+} rs_stream_src;
+
+typedef struct {
+    int fd;          /* output row: pwrite(fd, base + column offset) ... */
+    uint8_t *map;    /* ... or, when not NULL, memcpy into this shared mapping of the file (many rows of one
+                        file: positional writes to a single inode serialise in the kernel, stores do not) */
+    long long base;
+    int from_out;    /* 1: row `row` of the GPU output, 0: row `row` of the slab's input (pass-through) */
+    int row;
+    long long limit; /* logical length of this row in bytes (writes are clipped to it); < 0 = whole chunk */
+} rs_stream_dst;
+
+typedef struct {
+    int k, p;
+    int decode;                  /* 0: rsgpu_encode_host, 1: rsgpu_set_survivors + rsgpu_decode_erased_host */
+    const uint8_t *total_matrix; /* NULL: generate [I;V] on the GPU */
+    const int *survivors;        /* decode: k fragment indices in conf order */
+    uint8_t *matrix_out;         /* if not NULL: receives GPU 0's (k+p) x k total matrix */
+    int in_rows, out_rows;       /* rows read per slab, rows the GPU produces per slab */
+    long long chunk;             /* bytes per fragment */
+    const rs_stream_src *src;    /* in_rows entries */
+    const rs_stream_dst *dst;    /* n_dst entries */
+    int n_dst;
+    int grid_cap;                /* reference -p, 0 = default */
+    int slots;                   /* reference -s, <= 0 = default */
+    int io_threads;              /* <= 0 = default (8) */
+} rs_stream_desc;
+
+size_t rs_stream_slab_bytes(long long chunk, int rows, int n_gpus);
+/* returns 0 or the first RSGPU_E* code; error_text gets the message */
+int rs_stream_run(const rs_stream_desc *desc, double *wall_ms, int *n_gpus_used, char *error_text, size_t error_cap);
 
 #endif
