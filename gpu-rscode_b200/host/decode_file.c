@@ -76,6 +76,9 @@ void decode_file(char *inFile, char *confFile, char *outFile, int gridDimXSize, 
         src[i].base = 0; /* short fragment files read as zero-padded, src/decode.cu:290-291 */
     }
 
+    const int gpu_budget = rs_file_gpu_budget(md.total_size);
+    rs_limit_visible_gpus(gpu_budget); /* before the first CUDA call: start-up cost scales with visible GPUs */
+
     int maxGrid = 65535;
     struct timespec ts0, ts1;
     clock_gettime(CLOCK_MONOTONIC, &ts0);
@@ -137,6 +140,7 @@ void decode_file(char *inFile, char *confFile, char *outFile, int gridDimXSize, 
     d.n_dst = k;
     d.grid_cap = gridDimXSize;
     d.slots = streamNum;
+    d.max_gpus = gpu_budget;
     double wall_ms = 0;
     int used = 0;
     char err[512] = "";

@@ -39,6 +39,9 @@ void encode_file(char *fileName, int nativeBlockNum, int parityBlockNum, int gri
     const long long totalSize = (long long)sb.st_size;
     const long long chunk = rs_chunk_size(totalSize, k);
 
+    const int gpu_budget = rs_file_gpu_budget(totalSize);
+    rs_limit_visible_gpus(gpu_budget); /* before the first CUDA call: start-up cost scales with visible GPUs */
+
     int maxGrid = 65535;
     struct timespec ts0, ts1;
     clock_gettime(CLOCK_MONOTONIC, &ts0);
@@ -88,6 +91,7 @@ void encode_file(char *fileName, int nativeBlockNum, int parityBlockNum, int gri
     d.n_dst = k + p;
     d.grid_cap = gridDimXSize;
     d.slots = streamNum;
+    d.max_gpus = gpu_budget;
     double wall_ms = 0;
     int used = 0;
     char err[512] = "";

@@ -33,6 +33,8 @@ void rs_free_conf(rs_conf *conf);
 /* ---- sched.c : how a stripe is spread over the visible GPUs ---- */
 int rs_plan_gpus(size_t len, int visible);
 void rs_partition(size_t len, int parts, int g, size_t *off, size_t *n);
+int rs_file_gpu_budget(long long bytes);
+void rs_limit_visible_gpus(int n);
 
 /* ---- stream.c : streaming slab pipeline  file -> pinned ring -> GPU(s) -> files ---- */
 typedef struct {
@@ -64,6 +66,7 @@ typedef struct {
     int grid_cap;                /* reference -p, 0 = default */
     int slots;                   /* reference -s, <= 0 = default */
     int io_threads;              /* <= 0 = default (8) */
+    int max_gpus;                /* <= 0 = every visible GPU */
 } rs_stream_desc;
 
 size_t rs_stream_slab_bytes(long long chunk, int rows, int n_gpus);

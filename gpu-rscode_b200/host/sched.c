@@ -4,6 +4,9 @@
  * (src/encode.cu:357-403, src/decode.cu:335-378).  The pipeline that uses it is stream.c.
  */
 #include <stddef.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include "rs_host.h"
 
@@ -28,3 +31,54 @@ void rs_partition(size_t len, int parts, int g, size_t *off, size_t *n)
     *n = (g == parts - 1) ? len - *off : per;
 }
 
+
+/* How many GPUs a file job of `bytes` should start.  Measured on B200 boxes (tools/run_files.py,
+ * RS_TIMING=1): the host side of a file job (page-cache reads and writes through 8 IO threads) moves
+ * ~25 GB/s while ONE GPU's pinned H2D+D2H pipeline takes ~50 GB/s, and every additional visible GPU adds
+ * 0.6-0.9 s of driver / context start-up per process (4 GiB RS(32,40) encode: 1.78 s with one GPU visible,
+ * 3.32 s with two).  So unlike the reference, which starts a thread on every visible GPU
+ * (src/encode.cu:357-366), a file job uses one GPU per 32 GiB of input; RS_GPUS=<n> overrides. */
+int rs_file_gpu_budget(long long bytes)
+{
+    const char *e = getenv("RS_GPUS");
+    if (e && atoi(e) > 0)
+        return atoi(e);
+    const long long per_gpu = 32LL << 30;
+    long long n = (bytes + per_gpu - 1) / per_gpu;
+    return n < 1 ? 1 : (n > 64 ? 64 : (int)n);
+}
+
+/* Narrow CUDA_VISIBLE_DEVICES to the first `n` devices (of the user's list if there is one) so that the
+ * CUDA start-up of this process only pays for the GPUs it will use.  Only effective before the first
+ * CUDA call of the process; harmless afterwards (the pipeline caps its GPU count anyway). */
+void rs_limit_visible_gpus(int n)
+{
+    const char *cur = getenv("CUDA_VISIBLE_DEVICES");
+    char buf[1024];
+    size_t len = 0;
+    buf[0] = 0;
+    if (cur && *cur) {
+        int taken = 0;
+        const char *p = cur;
+        while (*p && taken < n) {
+            const char *q = strchr(p, ',');
+            size_t w = q ? (size_t)(q - p) : strlen(p);
+            if (len + w + 2 >= sizeof buf)
+                break;
+            if (taken)
+                buf[len++] = ',';
+            memcpy(buf + len, p, w);
+            len += w;
+            buf[len] = 0;
+            ++taken;
+            if (!q)
+                break;
+            p = q + 1;
+        }
+    } else {
+        for (int i = 0; i < n && len + 8 < sizeof buf; ++i)
+            len += (size_t)snprintf(buf + len, sizeof buf - len, i ? ",%d" : "%d", i);
+    }
+    if (buf[0])
+        setenv("CUDA_VISIBLE_DEVICES", buf, 1);
+}

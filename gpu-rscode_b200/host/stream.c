@@ -55,6 +55,7 @@ struct rs_stream {
     int error;
     char error_text[512];
     double gpu_ms[64];
+    double t_start;
 };
 
 static double now_s(void)
@@ -187,6 +188,8 @@ static void *gpu_main(void *arg)
     if (rc == RSGPU_OK && d->grid_cap > 0) rc = rsgpu_set_tuning(ctx, 0, 0, d->grid_cap);
     if (rc == RSGPU_OK && ga->gpu == 0 && d->matrix_out) rc = rsgpu_get_total_matrix(ctx, d->matrix_out);
     if (rc == RSGPU_OK && d->decode) rc = rsgpu_set_survivors(ctx, d->survivors);
+    if (getenv("RS_TIMING"))
+        fprintf(stderr, "[rs timing] GPU %d context + tables ready at +%.1f ms\n", ga->gpu, 1e3 * (now_s() - st->t_start));
     pthread_mutex_lock(&st->mu);
     if (rc != RSGPU_OK) {
         snprintf(text, sizeof text, "GPU %d: set-up failed: %s (%s)", ga->gpu, rsgpu_strerror(rc), rsgpu_last_error());
@@ -265,6 +268,7 @@ int rs_stream_run(const rs_stream_desc *desc, double *wall_ms, int *n_gpus_used,
         return rc != RSGPU_OK ? rc : RSGPU_ECUDA;
     }
     if (visible > 64) visible = 64;
+    if (desc->max_gpus > 0 && visible > desc->max_gpus) visible = desc->max_gpus;
     st.n_gpus = rs_plan_gpus((size_t)desc->chunk, visible);
     st.slab_bytes = rs_stream_slab_bytes(desc->chunk, desc->in_rows, st.n_gpus);
     st.n_slabs = desc->chunk > 0 ? (desc->chunk + (long long)st.slab_bytes - 1) / (long long)st.slab_bytes : 0;
@@ -301,6 +305,7 @@ int rs_stream_run(const rs_stream_desc *desc, double *wall_ms, int *n_gpus_used,
     pthread_t *gp = calloc((size_t)st.n_gpus, sizeof(pthread_t));
     gpu_arg_t *ga = calloc((size_t)st.n_gpus, sizeof(gpu_arg_t));
     const double t0 = now_s();
+    st.t_start = t0;
     for (int i = 0; i < st.n_io; ++i) pthread_create(&io[i], NULL, io_main, &st);
     for (int g = 0; g < st.n_gpus; ++g) {
         ga[g].st = &st;
@@ -333,9 +338,12 @@ int rs_stream_run(const rs_stream_desc *desc, double *wall_ms, int *n_gpus_used,
     pthread_cond_broadcast(&st.cv_ready);
     pthread_mutex_unlock(&st.mu);
 
+    const double t_pipe = now_s();
     for (int g = 0; g < st.n_gpus; ++g) pthread_join(gp[g], NULL);
     for (int i = 0; i < st.n_io; ++i) pthread_join(io[i], NULL);
-    if (wall_ms) *wall_ms = 1e3 * (now_s() - t0);
+    if (wall_ms) *wall_ms = 1e3 * (t_pipe - t0);
+    if (getenv("RS_TIMING"))
+        fprintf(stderr, "[rs timing] pipeline %.1f ms, context teardown %.1f ms\n", 1e3 * (t_pipe - t0), 1e3 * (now_s() - t_pipe));
     for (int g = 0; g < st.n_gpus; ++g)
         printf("Device%d: Total GPU %s time: %fms\n", g, desc->decode ? "decoding" : "encoding", st.gpu_ms[g]);
 

@@ -111,3 +111,32 @@ def test_world2_gloo_stripe_sharding_matches_single_process():
         for s in range(n_stripes))
     assert digests == want
     assert sharding.job_throughput_gbs(k * L, world, 3, 11.0) == pytest.approx(2 * k * L * 3 / 0.011 / 1e9)
+
+
+def test_file_gpu_budget_and_visible_device_narrowing():
+    """host/sched.c: one GPU per 32 GiB of file unless RS_GPUS says otherwise; CUDA_VISIBLE_DEVICES is
+    narrowed to the first n (of the user's list if any).  Run in a child: it edits the environment."""
+    import subprocess
+    import sys
+    code = r'''
+import ctypes, os, sys
+os.environ.pop("CUDA_VISIBLE_DEVICES", None); os.environ.pop("RS_GPUS", None)
+ctypes.CDLL(sys.argv[1], mode=ctypes.RTLD_GLOBAL)
+H = ctypes.CDLL(sys.argv[2])
+H.rs_file_gpu_budget.argtypes = [ctypes.c_longlong]
+libc = ctypes.CDLL(None); libc.getenv.restype = ctypes.c_char_p
+assert H.rs_file_gpu_budget(0) == 1 and H.rs_file_gpu_budget(64 << 20) == 1
+assert H.rs_file_gpu_budget(32 << 30) == 1 and H.rs_file_gpu_budget((32 << 30) + 1) == 2
+assert H.rs_file_gpu_budget(1 << 40) == 32
+libc.setenv(b"RS_GPUS", b"8", 1)
+assert H.rs_file_gpu_budget(10) == 8
+H.rs_limit_visible_gpus(3); assert libc.getenv(b"CUDA_VISIBLE_DEVICES") == b"0,1,2"
+libc.setenv(b"CUDA_VISIBLE_DEVICES", b"4,5,6,7", 1); H.rs_limit_visible_gpus(2)
+assert libc.getenv(b"CUDA_VISIBLE_DEVICES") == b"4,5"
+libc.setenv(b"CUDA_VISIBLE_DEVICES", b"6", 1); H.rs_limit_visible_gpus(4)
+assert libc.getenv(b"CUDA_VISIBLE_DEVICES") == b"6"
+print("ok")
+'''
+    r = subprocess.run([sys.executable, "-c", code, rs.LIB_PATH, rs.HOST_LIB_PATH], stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout

@@ -34,7 +34,7 @@ def run(cmd, cwd):
 
 
 def printed_ms(out, what):
-    m = re.search(r"Total (?:GPU|CPU) %s time(?: using multiple devices)?: ([0-9.]+)ms" % what, out)
+    m = re.search(r"^Total (?:GPU|CPU) %s time(?: using multiple devices)?: ([0-9.]+)ms" % what, out, re.M)
     return float(m.group(1)) if m else None
 
 
