@@ -20,8 +20,6 @@
 // the data word, scales it by 128 and adds the lane base in ONE fmaheavy-pipe instruction, no mask, no
 // shift (fat7 masks the word with 0x7F7F7F7F once per four bytes).  The per-fragment table offset is a
 // compile-time immediate of the LDS.
-#include <stdlib.h>
-
 #include "rs_internal.h"
 
 namespace rsgpu {
@@ -282,17 +280,33 @@ k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__rest
     const int tid = threadIdx.x, nt = blockDim.x;
 
     // ---- build the tables of this block from the 32-entry global tables (lo 16 + hi 16 per fragment) ----
-    for (int j = 0; j < M::NF; ++j) {
-        const int nx = j < M::N8 ? 256 : 128;
-        const uint32_t base = tb + M::off(j);
-        const uint32_t *tj = tab + (size_t)j * 32 * WW;
-        for (int i = tid; i < nx * REP; i += nt) {
-            const int x = i / REP, r = i - x * REP;
-#pragma unroll
-            for (int q = 0; q < WW; ++q) {
-                const uint32_t v = __ldg(tj + (x & 15) * WW + q) ^ __ldg(tj + (16 + (x >> 4)) * WW + q);
-                asm volatile("st.shared.u32 [%0], %1;" ::"r"(base + x * 128 + r * W + q * 4), "r"(v) : "memory");
+    // One flat loop over 16-byte stores (4 replicas of a 4-byte entry, 2 of an 8-byte entry) so that every
+    // thread has several independent table reads in flight; the 32-entry tables (k * 32 * W bytes) stay
+    // L1-resident after the first touch.  ~1-2 us per block instead of ~8 us for per-fragment loops.
+    {
+        constexpr int RV = REP * W / 16;                 // 16-byte stores per table row (= 8)
+        constexpr int V8 = 256 * RV, V7 = 128 * RV;      // stores per fat8 / fat7 table
+        constexpr int TOTAL = M::N8 * V8 + (M::NF - M::N8) * V7;
+#pragma unroll 4
+        for (int i = tid; i < TOTAL; i += nt) {
+            int j, rem;
+            if (i < M::N8 * V8) {
+                j = i / V8;
+                rem = i - j * V8;
+            } else {
+                const int i2 = i - M::N8 * V8;
+                j = i2 / V7;
+                rem = i2 - j * V7;
+                j += M::N8;
             }
+            const int x = rem / RV, r = rem - x * RV;
+            const uint32_t *tj = tab + (size_t)j * 32 * WW;
+            const uint32_t v0 = __ldg(tj + (x & 15) * WW) ^ __ldg(tj + (16 + (x >> 4)) * WW);
+            uint32_t v1 = v0;
+            if constexpr (W == 8) v1 = __ldg(tj + (x & 15) * WW + 1) ^ __ldg(tj + (16 + (x >> 4)) * WW + 1);
+            const uint32_t base = tb + (j < M::N8 ? j * 32768 : M::N8 * 32768 + (j - M::N8) * 16384);
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(base + x * 128 + r * 16), "r"(v0), "r"(v1),
+                         "r"(v0), "r"(v1) : "memory");
         }
     }
     for (int i = tid; i < (K - M::NF) * 32 * WW; i += nt) {   // thin pages: straight copy, 256-byte stride
@@ -338,24 +352,11 @@ struct FatKernel {
 template <int W, int JB, int KB>
 FatKernel make_fat()
 {
-    // L2 prefetch one stride ahead: on from k = 8 (measured: RS(10,14) 0.83 -> 0.96, RS(8,12) 0.905 -> 0.921,
-    // RS(4,6) 0.99 -> 0.87 of the peak)
+    // L2 prefetch one stride ahead: on from k = 8.  Same box, same build, off -> on (fraction of the measured
+    // HBM peak): RS(8,12) 0.894 -> 0.934, RS(10,14) 0.896 -> 0.991, RS(12,16) 0.866 -> 0.913, RS(14,18) 0.796 ->
+    // 0.893, RS(16,20) 0.885 -> 0.928, RS(20,24) 0.824 -> 0.858; but RS(6,9) 0.970 -> 0.906, RS(4,6) 0.99 -> 0.87.
     constexpr bool PF = (JB * KB >= 8);
-    static const int pf_env = getenv("RSGPU_PF") ? atoi(getenv("RSGPU_PF")) : -1;   // developer override
-    const bool pf = pf_env >= 0 ? pf_env != 0 : PF;
-    return FatKernel{pf ? k_gf_matmul_fat<W, JB, KB, true> : k_gf_matmul_fat<W, JB, KB, false>, fat_threads(W, JB),
-                     Map<JB * KB>::BYTES + 256};
-}
-
-template <int W>
-bool pick_fat_alt(int k, FatKernel *fk)   // developer experiment (RSGPU_FAT_ALT): other batch shapes
-{
-    switch (k) {
-    case 10: *fk = make_fat<W, 5, 2>(); return true;
-    case 14: *fk = make_fat<W, 2, 7>(); return true;
-    case 20: *fk = make_fat<W, 4, 5>(); return true;
-    default: return false;
-    }
+    return FatKernel{k_gf_matmul_fat<W, JB, KB, PF>, fat_threads(W, JB), Map<JB * KB>::BYTES + 256};
 }
 
 // Batch shape per k (JB fragments per batch x KB batches), measured on B200: batches of 4 with 768
@@ -364,11 +365,14 @@ bool pick_fat_alt(int k, FatKernel *fk)   // developer experiment (RSGPU_FAT_ALT
 template <int W>
 bool pick_fat(int k, FatKernel *fk)
 {
-    static const bool alt = getenv("RSGPU_FAT_ALT") != nullptr;
-    if (alt && pick_fat_alt<W>(k, fk)) return true;
     switch (k) {
+    case 3: *fk = make_fat<W, 3, 1>(); return true;
     case 4: *fk = make_fat<W, 4, 1>(); return true;
+    case 5: *fk = make_fat<W, 5, 1>(); return true;
     case 6: *fk = make_fat<W, 6, 1>(); return true;
+    case 9: *fk = make_fat<W, 3, 3>(); return true;
+    case 15: *fk = make_fat<W, 5, 3>(); return true;
+    case 18: *fk = make_fat<W, 3, 6>(); return true;
     case 8: *fk = make_fat<W, 4, 2>(); return true;
     case 10: *fk = make_fat<W, 2, 5>(); return true;
     case 12: *fk = make_fat<W, 4, 3>(); return true;

@@ -81,9 +81,9 @@ template <> __device__ __forceinline__ void acc_clear<8>(Acc<8> &acc)
 // EX = 0: one PRMT per lookup splices the byte into the page-base register (page bases have
 //          a zero low byte), so the address costs a single alu-pipe instruction and the LDS needs no
 //          immediate.  The +16*W of the high table is OR-ed into the mask step.
-// EX = 1: shift + mask per nibble, then an add of the page base.
 // EX = 2 (default): one DP4A per lookup (dot product with a one-hot byte selector, accumulating onto the base).
-// EX = 3: low nibbles as EX 0, high nibbles as EX 2 -- splits the work over two pipes.
+// (Two more were measured and dropped: shift+mask per nibble, 1.48 ms vs 1.18 ms on RS(10,14); and a
+// PRMT/DP4A mix, 1.23 ms.)
 template <int W, int EX>
 __device__ __forceinline__ void mac_word(uint32_t w, uint32_t tj, uint32_t hi4, Acc<W> &acc, int pos0)
 {
@@ -92,32 +92,22 @@ __device__ __forceinline__ void mac_word(uint32_t w, uint32_t tj, uint32_t hi4, 
     constexpr uint32_t M4 = M1 * 0x01010101u;       // four of them
     constexpr uint32_t HI1 = 16u * W;               // offset of the high-nibble table inside the page
     uint32_t olo[4], ohi[4];
-    if constexpr (EX == 1) {
+    const uint32_t wl = (w << SH) & M4;
+    if constexpr (EX == 0) {
+        // hi4 == HI4, but it arrives as a kernel argument: a value the compiler cannot fold keeps
+        // (x & M4) | hi4 as ONE three-input LOP3 instead of an AND-immediate plus an OR-immediate
+        const uint32_t wh = ((w >> (4 - SH)) & M4) | hi4;
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
-            // low nibble of byte b sits at bit 8b, wanted at bit SH: shift right by 8b-SH (left for b = 0)
-            const uint32_t lo = (b == 0) ? (w << SH) : (w >> (8 * b - SH));
-            olo[b] = tj + (lo & M1);
-            ohi[b] = tj + HI1 + ((w >> (8 * b + 4 - SH)) & M1);
+            olo[b] = __byte_perm(wl, tj, 0x7650u + b);
+            ohi[b] = __byte_perm(wh, tj, 0x7650u + b);
         }
     } else {
-        const uint32_t wl = (w << SH) & M4;
-        if constexpr (EX == 0) {
-            // hi4 == HI4, but it arrives as a kernel argument: a value the compiler cannot fold keeps
-            // (x & M4) | hi4 as ONE three-input LOP3 instead of an AND-immediate plus an OR-immediate
-            const uint32_t wh = ((w >> (4 - SH)) & M4) | hi4;
+        const uint32_t wh = (w >> (4 - SH)) & M4;
 #pragma unroll
-            for (int b = 0; b < 4; ++b) {
-                olo[b] = __byte_perm(wl, tj, 0x7650u + b);
-                ohi[b] = __byte_perm(wh, tj, 0x7650u + b);
-            }
-        } else {
-            const uint32_t wh = (w >> (4 - SH)) & M4;
-#pragma unroll
-            for (int b = 0; b < 4; ++b) {
-                olo[b] = (EX == 2) ? __dp4a(wl, 1u << (8 * b), tj) : __byte_perm(wl, tj, 0x7650u + b);
-                ohi[b] = __dp4a(wh, 1u << (8 * b), tj + HI1);
-            }
+        for (int b = 0; b < 4; ++b) {
+            olo[b] = __dp4a(wl, 1u << (8 * b), tj);
+            ohi[b] = __dp4a(wh, 1u << (8 * b), tj + HI1);
         }
     }
 #pragma unroll
@@ -271,35 +261,37 @@ MatmulFn pick_jb(int jb, bool pad)
     case 1: return k_gf_matmul<W, 1, EX, false>;
     case 2: return k_gf_matmul<W, 2, EX, false>;
     case 3: return k_gf_matmul<W, 3, EX, false>;
-    case 4: return k_gf_matmul<W, 4, EX, false>;
-    case 5: return k_gf_matmul<W, 5, EX, false>;
-    case 6: return k_gf_matmul<W, 6, EX, false>;
-    case 7: return k_gf_matmul<W, 7, EX, false>;
+    case 4: return pad ? k_gf_matmul<W, 4, EX, true> : k_gf_matmul<W, 4, EX, false>;
+    case 5: return pad ? k_gf_matmul<W, 5, EX, true> : k_gf_matmul<W, 5, EX, false>;
+    case 6: return pad ? k_gf_matmul<W, 6, EX, true> : k_gf_matmul<W, 6, EX, false>;
+    case 7: return pad ? k_gf_matmul<W, 7, EX, true> : k_gf_matmul<W, 7, EX, false>;
     default: return pad ? k_gf_matmul<W, 8, EX, true> : k_gf_matmul<W, 8, EX, false>;
     }
 }
 
-MatmulFn pick_kernel(int width, int jb, int ex, bool pad)
+MatmulFn pick_kernel(int width, int jb, bool prmt, bool pad)
 {
-    if (width == 4) {
-        if (ex == 1) return pick_jb<4, 1>(jb, pad);
-        if (ex == 2) return pick_jb<4, 2>(jb, pad);
-        if (ex == 3) return pick_jb<4, 3>(jb, pad);
-        return pick_jb<4, 0>(jb, pad);
-    }
-    if (ex == 1) return pick_jb<8, 1>(jb, pad);
-    if (ex == 2) return pick_jb<8, 2>(jb, pad);
-    if (ex == 3) return pick_jb<8, 3>(jb, pad);
-    return pick_jb<8, 0>(jb, pad);
+    if (width == 4) return prmt ? pick_jb<4, 0>(jb, pad) : pick_jb<4, 2>(jb, pad);
+    return prmt ? pick_jb<8, 0>(jb, pad) : pick_jb<8, 2>(jb, pad);
 }
 
-// Fragments per load batch: the largest divisor of k in 4..8 (no padded fragments), else 8 (or k).
+// Fragments per load batch.  A divisor of k in 3..8 if there is one (largest first): no padded slots.
+// Otherwise (primes above 8, ...) the batch size in 4..8 that wastes the fewest padded slots; the slots
+// behind k re-read the last row against all-zero tables, so waste costs time, not correctness.
 int choose_jb(int k)
 {
     if (k <= 8) return k;
-    for (int jb = 8; jb >= 4; --jb)
+    for (int jb = 8; jb >= 3; --jb)
         if (k % jb == 0) return jb;
-    return 8;
+    int best = 8, best_waste = 1 << 30;
+    for (int jb = 8; jb >= 4; --jb) {
+        const int waste = (k + jb - 1) / jb * jb - k;
+        if (waste < best_waste) {
+            best = jb;
+            best_waste = waste;
+        }
+    }
+    return best;
 }
 
 }  // namespace
@@ -316,10 +308,10 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
     const int threads = (tune.threads > 0 && tune.threads <= 256) ? tune.threads : 256;
 
     // variant 0 (default): the bank-replicated kernel when an instance exists for this k and the stripe
-    // is long enough to pay for building its tables (one 227 KiB fill per SM, ~8 us: measured break-even
-    // on B200 at 16 MiB per fragment for RS(10,14)); 5 forces it, 6 forbids it
+    // is long enough to pay for building its tables (one 227 KiB fill per SM: measured break-even
+    // on B200 at 4-8 MiB per fragment for RS(10,14)); 5 forces it, 6 forbids it
     bool done_vec = false;
-    if (nvec && (tune.variant == 5 || (tune.variant == 0 && len >= ((size_t)12 << 20)))) {
+    if (nvec && (tune.variant == 5 || (tune.variant == 0 && len >= ((size_t)8 << 20)))) {
         cudaError_t e = launch_matmul_fat(g, k, in, in_pitch, out_g, out_pitch, nvec, dev, tune.max_blocks, tune.threads, s);
         if (e == cudaSuccess) {
             done_vec = true;
@@ -330,11 +322,11 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
     }
     if (nvec && !done_vec) {
         const int jb = choose_jb(k);
-        const int kb = (k + jb - 1) / jb;           // kb*jb <= kpad because kpad is k rounded up to 8
-        // variant 0 = default = DP4A extraction (EX 2): same speed as the PRMT splice on B200 but it
-        // leaves the alu pipe at 45% instead of 81% (ncu, profiles/r1_pipes.md); 1..4 select EX 0..3
-        const int ex = (tune.variant == 0 || tune.variant > 4) ? 2 : (tune.variant - 1) % 4;
-        MatmulFn fn = pick_kernel(g.width, jb, ex, kb * jb > k);
+        const int kb = (k + jb - 1) / jb;           // kb*jb <= kpad: choose_jb never wastes more than jb = 8 does
+        if (kb * jb > kpad) return cudaErrorInvalidValue;
+        // index extraction: DP4A (default; same speed as the PRMT splice on B200 but the alu pipe sits at
+        // 45 % instead of 81 %, profiles/r1_pipes_variant*.csv); variant 1 selects the PRMT splice
+        MatmulFn fn = pick_kernel(g.width, jb, tune.variant == 1, kb * jb > k);
         const size_t smem = (size_t)kpad * 256 + 256;   // one page per fragment + alignment slack
         if (smem > 48 * 1024) {
             cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
