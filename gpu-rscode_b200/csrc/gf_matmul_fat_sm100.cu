@@ -41,10 +41,6 @@ __host__ __device__ constexpr int fat8_count(int k)
     int n8 = left / 16384;
     return n8 > n ? n : n8;
 }
-__host__ __device__ constexpr int fat_smem_bytes(int k)
-{
-    return fat_count(k) * 16384 + fat8_count(k) * 16384 + (k - fat_count(k)) * 256;
-}
 __host__ __device__ constexpr int fat_threads(int W, int JB)
 {
     // register budget: accumulators (16 or 32) + two batches of JB vectors

@@ -81,4 +81,11 @@ cudaError_t launch_matmul_fat(const RowGroup &g, int k, const uint8_t *in, size_
                               size_t out_pitch, size_t nvec, const DeviceInfo &dev, int max_blocks, int threads,
                               cudaStream_t s);
 
+
+// ---- gf_matmul_tma_sm100.cu ---------------------------------------------------------------------
+// Split-nibble kernel fed by TMA bulk copies through a shared-memory stage ring (tuning variant 7).
+// cudaErrorNotSupported when k has no divisor among the compiled batch sizes.
+cudaError_t launch_matmul_tma(const RowGroup &g, int k, int kpad, const uint8_t *in, size_t in_pitch, uint8_t *out_g,
+                              size_t out_pitch, size_t nvec, const DeviceInfo &dev, int max_blocks, cudaStream_t s);
+
 }  // namespace rsgpu

@@ -121,8 +121,9 @@ def test_encode_vs_oracle(rs, orc, torch, k, p, L):
     assert (got == want).all()
 
 
-@pytest.mark.parametrize("variant", [0, 1, 5, 6])  # auto, nibble tables with PRMT splice, byte tables, nibble tables (DP4A)
-@pytest.mark.parametrize("k,p,L", [(10, 4, 200_000), (32, 8, 50_000), (11, 3, 40_001), (13, 5, 160_000), (19, 2, 64_000), (23, 8, 32_000)])
+@pytest.mark.parametrize("variant", [0, 1, 5, 6, 7])  # auto, nibble+PRMT, byte tables, nibble+DP4A, nibble fed by TMA
+@pytest.mark.parametrize("k,p,L", [(10, 4, 200_000), (32, 8, 50_000), (11, 3, 40_001), (13, 5, 160_000), (19, 2, 64_000), (23, 8, 32_000),
+                                     (16, 4, 70_000 * 16), (5, 2, 4096 * 16 + 48), (4, 8, 100_000)])
 def test_encode_variants_vs_oracle(rs, orc, torch, variant, k, p, L):
     data = splitmix64_bytes(77 + variant, k * L).reshape(k, L)
     with rs.RSContext(k, p) as ctx:
