@@ -36,7 +36,7 @@ ABI_SYMBOLS = [
     "rsgpu_invert_matrix", "rsgpu_matmul", "rsgpu_encode_host", "rsgpu_decode_host", "rsgpu_decode_erased_host", "rsgpu_host_alloc",
     "rsgpu_host_free", "rsgpu_host_register", "rsgpu_host_unregister", "rsgpu_dev_alloc", "rsgpu_dev_free",
     "rsgpu_memcpy_h2d", "rsgpu_memcpy_d2h", "rsgpu_sync", "rsgpu_set_tuning", "rsgpu_launch_count",
-    "rsgpu_encode_noalloc",
+    "rsgpu_encode_noalloc", "rsgpu_create_generator", "rsgpu_set_repair", "rsgpu_repair",
 ]
 
 
@@ -75,6 +75,9 @@ def lib():
     L.rsgpu_device_max_grid.argtypes = [i32, C.POINTER(i32)]
     L.rsgpu_create.argtypes = [C.POINTER(vp), i32, i32, i32]
     L.rsgpu_create_with_matrix.argtypes = [C.POINTER(vp), i32, i32, i32, u8p]
+    L.rsgpu_create_generator.argtypes = [C.POINTER(vp), i32, i32, i32, i32]
+    L.rsgpu_set_repair.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), i32]
+    L.rsgpu_repair.argtypes = [vp, u8p, sz, u8p, sz, sz, vp]
     L.rsgpu_destroy.argtypes = [vp]
     L.rsgpu_destroy.restype = None
     for f in ("rsgpu_k", "rsgpu_p", "rsgpu_device"):
@@ -143,10 +146,13 @@ class RSContext:
     ``torch.cuda.current_stream().cuda_stream``.
     """
 
-    def __init__(self, k, p, device=0, total_matrix=None):
+    def __init__(self, k, p, device=0, total_matrix=None, generator=None):
         self._h = C.c_void_p(None)
         L = lib()
-        if total_matrix is None:
+        if generator is not None:
+            kind = {"vandermonde": 0, "cauchy": 1}[generator] if isinstance(generator, str) else int(generator)
+            _check(L.rsgpu_create_generator(C.byref(self._h), device, k, p, kind))
+        elif total_matrix is None:
             _check(L.rsgpu_create(C.byref(self._h), device, k, p))
         else:
             tm = np.ascontiguousarray(total_matrix, np.uint8)
@@ -194,6 +200,14 @@ class RSContext:
         n = C.c_int(0)
         _check(lib().rsgpu_get_erased(self._h, arr, C.byref(n)))
         return [arr[i] for i in range(n.value)]
+
+    def set_repair(self, survivors, wanted):
+        sv = (C.c_int * self.k)(*[int(i) for i in survivors])
+        wt = (C.c_int * len(wanted))(*[int(i) for i in wanted])
+        _check(lib().rsgpu_set_repair(self._h, sv, wt, len(wanted)))
+
+    def repair(self, surv_d, surv_pitch, out_d, out_pitch, length, stream=0):
+        _check(lib().rsgpu_repair(self._h, _ptr(surv_d), surv_pitch, _ptr(out_d), out_pitch, length, stream))
 
     def invert_matrix(self, M):
         M = np.ascontiguousarray(M, np.uint8)

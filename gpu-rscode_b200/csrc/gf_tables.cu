@@ -59,6 +59,46 @@ cudaError_t launch_gen_total_matrix(uint8_t *d_total, int k, int p, const GfTabl
     return cudaGetLastError();
 }
 
+// Cauchy generator (not in the reference): [I_k ; C], C[i][j] = 1 / (x_i + y_j) with
+// x_i = k + i and y_j = j -- all distinct for k + p <= 256, so every k x k sub-matrix of [I ; C] is
+// invertible (MDS), which [I ; V] is not.
+__global__ void k_gen_total_matrix_cauchy(uint8_t *total, int k, int p, const uint8_t *exp, const uint8_t *log)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (k + p) * k) return;
+    const int r = idx / k, j = idx - r * k;
+    total[idx] = (r < k) ? (uint8_t)(r == j) : (uint8_t)gf_inv(exp, log, (unsigned)(r ^ j));   // r = k + i
+}
+
+cudaError_t launch_gen_total_matrix_cauchy(uint8_t *d_total, int k, int p, const GfTables &gf, cudaStream_t s)
+{
+    const int n = (k + p) * k;
+    k_gen_total_matrix_cauchy<<<(n + 255) / 256, 256, 0, s>>>(d_total, k, p, gf.d_exp, gf.d_log);
+    return cudaGetLastError();
+}
+
+// C (rows x k) = A[sel[0..rows)] (rows of an (n x k) matrix) * B (k x k): the repair matrix
+// T[wanted] * inverse(T[survivors]).  Tiny (<= 255 x 255 x 255), one thread per output entry.
+__global__ void k_rows_times_matrix(const uint8_t *A, const int *sel, int rows, const uint8_t *B, int k, uint8_t *C,
+                                    const uint8_t *exp, const uint8_t *log)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= rows * k) return;
+    const int i = idx / k, j = idx - i * k;
+    const uint8_t *a = A + (size_t)sel[i] * k;
+    unsigned acc = 0;
+    for (int t = 0; t < k; ++t) acc ^= gf_mul(exp, log, a[t], B[(size_t)t * k + j]);
+    C[idx] = (uint8_t)acc;
+}
+
+cudaError_t launch_rows_times_matrix(const uint8_t *d_A, const int *d_sel, int rows, const uint8_t *d_B, int k,
+                                     uint8_t *d_C, const GfTables &gf, cudaStream_t s)
+{
+    const int n = rows * k;
+    k_rows_times_matrix<<<(n + 127) / 128, 128, 0, s>>>(d_A, d_sel, rows, d_B, k, d_C, gf.d_exp, gf.d_log);
+    return cudaGetLastError();
+}
+
 // Row i of the k x k decode input = row rows[i] of the total matrix (reference copy_matrix,
 // src/decode.cu:75-81,307).
 __global__ void k_gather_rows(const uint8_t *total, int k, const int *rows, int nrows, uint8_t *out)

@@ -21,6 +21,8 @@ struct rsgpu_ctx {
     rsgpu::Plan dec_full;         // k x k inverse (reference-semantic decode)
     rsgpu::Plan dec_erased;       // e x k rows of the inverse for the erased natives
     rsgpu::Plan scratch;          // rsgpu_matmul's caller-supplied matrix
+    rsgpu::Plan repair;           // m x k: T[wanted] * inverse, rebuilds any wanted fragments
+    bool have_repair = false;
 
     bool have_survivors = false;
     int survivors[256];

@@ -52,6 +52,9 @@ struct Tuning {
 // ---- gf_tables.cu ---------------------------------------------------------------------------
 cudaError_t launch_build_gf_tables(uint8_t *d_exp, uint8_t *d_log, cudaStream_t s);
 cudaError_t launch_gen_total_matrix(uint8_t *d_total, int k, int p, const GfTables &gf, cudaStream_t s);
+cudaError_t launch_gen_total_matrix_cauchy(uint8_t *d_total, int k, int p, const GfTables &gf, cudaStream_t s);
+cudaError_t launch_rows_times_matrix(const uint8_t *d_A, const int *d_sel, int rows, const uint8_t *d_B, int k,
+                                     uint8_t *d_C, const GfTables &gf, cudaStream_t s);
 cudaError_t launch_gather_rows(const uint8_t *d_total, int k, const int *d_rows, int nrows,
                                uint8_t *d_out, cudaStream_t s);
 cudaError_t launch_build_product_tables(const uint8_t *d_matrix, int k, int kpad, int row0, int nrows,

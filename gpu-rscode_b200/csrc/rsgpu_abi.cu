@@ -102,11 +102,13 @@ int ctx_bind(const rsgpu_ctx *c)
     return RSGPU_OK;
 }
 
-static int ctx_create(rsgpu_ctx **out, int device, int k, int p, const uint8_t *total)
+static int ctx_create(rsgpu_ctx **out, int device, int k, int p, const uint8_t *total, int generator = RSGPU_GEN_VANDERMONDE)
 {
     if (!out) return fail_msg(RSGPU_EINVAL, "out is NULL");
     *out = nullptr;
     if (k < 1 || k > RSGPU_MAX_K || p < 0 || p > 255) return fail_msg(RSGPU_EINVAL, "need 1 <= k <= 255, 0 <= p <= 255");
+    if (generator != RSGPU_GEN_VANDERMONDE && generator != RSGPU_GEN_CAUCHY) return fail_msg(RSGPU_EINVAL, "unknown generator kind");
+    if (generator == RSGPU_GEN_CAUCHY && k + p > 256) return fail_msg(RSGPU_EINVAL, "a Cauchy generator needs k + p <= 256");
     int ndev = 0;
     CK(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) return fail_msg(RSGPU_EINVAL, "no such CUDA device");
@@ -143,7 +145,9 @@ static int ctx_create(rsgpu_ctx **out, int device, int k, int p, const uint8_t *
         if ((e = cudaMemcpyAsync(c->d_total, total, (size_t)(k + p) * k, cudaMemcpyHostToDevice, s)) != cudaSuccess)
             return bail(fail_cuda(e, "copy total matrix"));
     } else {
-        if ((e = launch_gen_total_matrix(c->d_total, k, p, c->gf, s)) != cudaSuccess) return bail(fail_cuda(e, "gen_total_matrix"));
+        e = generator == RSGPU_GEN_CAUCHY ? launch_gen_total_matrix_cauchy(c->d_total, k, p, c->gf, s)
+                                          : launch_gen_total_matrix(c->d_total, k, p, c->gf, s);
+        if (e != cudaSuccess) return bail(fail_cuda(e, "gen_total_matrix"));
         ++c->launches;
     }
     if (p > 0) {
@@ -203,6 +207,11 @@ int rsgpu_create_with_matrix(rsgpu_ctx **out, int device, int k, int p, const ui
     return ctx_create(out, device, k, p, total_matrix);
 }
 
+int rsgpu_create_generator(rsgpu_ctx **out, int device, int k, int p, int generator)
+{
+    return ctx_create(out, device, k, p, nullptr, generator);
+}
+
 void rsgpu_destroy(rsgpu_ctx *c)
 {
     if (!c) return;
@@ -212,6 +221,7 @@ void rsgpu_destroy(rsgpu_ctx *c)
     plan_free(c->dec_full);
     plan_free(c->dec_erased);
     plan_free(c->scratch);
+    plan_free(c->repair);
     if (c->gf.d_exp) cudaFree(c->gf.d_exp);
     if (c->d_total) cudaFree(c->d_total);
     if (c->d_sub) cudaFree(c->d_sub);
@@ -288,6 +298,41 @@ int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
     CK(cudaStreamSynchronize(s));
     c->have_survivors = true;
     return RSGPU_OK;
+}
+
+int rsgpu_set_repair(rsgpu_ctx *c, const int *survivors, const int *wanted, int n_wanted)
+{
+    if (!c || !survivors || !wanted) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (n_wanted < 1 || n_wanted > 255) return fail_msg(RSGPU_EINVAL, "need 1 <= n_wanted <= 255");
+    for (int i = 0; i < n_wanted; ++i)
+        if (wanted[i] < 0 || wanted[i] >= c->k + c->p) return fail_msg(RSGPU_EINVAL, "wanted fragment index out of range");
+    c->have_repair = false;
+    int rc = rsgpu_set_survivors(c, survivors);   // inverse of the survivor rows (may be RSGPU_ESINGULAR)
+    if (rc != RSGPU_OK) return rc;
+    const int k = c->k;
+    cudaStream_t s = c->setup_stream;
+    if (c->repair.rows != n_wanted || !c->repair.d_matrix)
+        if ((rc = plan_alloc(c->repair, n_wanted, k)) != RSGPU_OK) return rc;
+    // repair matrix = (rows `wanted` of the total matrix) x inverse: natives come out as rows of the
+    // inverse, parities as generator rows applied to the reconstructed natives, in one multiply
+    CK(cudaMemcpyAsync(c->d_rows, wanted, sizeof(int) * n_wanted, cudaMemcpyHostToDevice, s));
+    CK(launch_rows_times_matrix(c->d_total, c->d_rows, n_wanted, c->dec_full.d_matrix, k, c->repair.d_matrix, c->gf, s));
+    ++c->launches;
+    if ((rc = plan_build_tables(c, c->repair, s)) != RSGPU_OK) return rc;
+    CK(cudaStreamSynchronize(s));
+    c->have_repair = true;
+    return RSGPU_OK;
+}
+
+int rsgpu_repair(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, uint8_t *out_d, size_t out_pitch, size_t len,
+                 void *stream)
+{
+    if (!c || !surv_d || !out_d) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (!c->have_repair) return fail_msg(RSGPU_ESTATE, "rsgpu_set_repair has not succeeded yet");
+    if ((c->k > 1 && surv_pitch < len) || (c->repair.rows > 1 && out_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    return plan_apply(c, c->repair, surv_d, surv_pitch, out_d, out_pitch, len, (cudaStream_t)stream);
 }
 
 int rsgpu_get_decode_matrix(rsgpu_ctx *c, uint8_t *inverse)

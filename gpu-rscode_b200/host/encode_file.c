@@ -82,6 +82,10 @@ void encode_file(char *fileName, int nativeBlockNum, int parityBlockNum, int gri
     d.k = k;
     d.p = p;
     d.decode = 0;
+    /* RS_GENERATOR=cauchy: MDS generator instead of the reference's Vandermonde rows; the matrix goes
+     * into METADATA, which is what this engine's decoder (and the reference's GPU decoder) reads */
+    const char *gen = getenv("RS_GENERATOR");
+    d.generator = (gen && !strcmp(gen, "cauchy")) ? RSGPU_GEN_CAUCHY : RSGPU_GEN_VANDERMONDE;
     d.matrix_out = total;
     d.in_rows = k;
     d.out_rows = p;

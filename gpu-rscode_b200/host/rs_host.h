@@ -55,7 +55,8 @@ typedef struct {
 typedef struct {
     int k, p;
     int decode;                  /* 0: rsgpu_encode_host, 1: rsgpu_set_survivors + rsgpu_decode_erased_host */
-    const uint8_t *total_matrix; /* NULL: generate [I;V] on the GPU */
+    const uint8_t *total_matrix; /* NULL: generate the total matrix on the GPU */
+    int generator;               /* when generating: RSGPU_GEN_VANDERMONDE (reference) or RSGPU_GEN_CAUCHY */
     const int *survivors;        /* decode: k fragment indices in conf order */
     uint8_t *matrix_out;         /* if not NULL: receives GPU 0's (k+p) x k total matrix */
     int in_rows, out_rows;       /* rows read per slab, rows the GPU produces per slab */

@@ -184,7 +184,7 @@ static void *gpu_main(void *arg)
     rsgpu_ctx *ctx = NULL;
     char text[512];
     int rc = d->total_matrix ? rsgpu_create_with_matrix(&ctx, ga->gpu, d->k, d->p, d->total_matrix)
-                             : rsgpu_create(&ctx, ga->gpu, d->k, d->p);
+                             : rsgpu_create_generator(&ctx, ga->gpu, d->k, d->p, d->generator);
     if (rc == RSGPU_OK && d->grid_cap > 0) rc = rsgpu_set_tuning(ctx, 0, 0, d->grid_cap);
     if (rc == RSGPU_OK && ga->gpu == 0 && d->matrix_out) rc = rsgpu_get_total_matrix(ctx, d->matrix_out);
     if (rc == RSGPU_OK && d->decode) rc = rsgpu_set_survivors(ctx, d->survivors);

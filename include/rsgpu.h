@@ -63,6 +63,19 @@ int rsgpu_create(rsgpu_ctx **out, int device, int k, int p);
  */
 int rsgpu_create_with_matrix(rsgpu_ctx **out, int device, int k, int p, const uint8_t *total_matrix);
 
+/*
+ * Same as rsgpu_create with a choice of generator.  RSGPU_GEN_VANDERMONDE is the reference's
+ * V[i][j] = (j+1)^i (src/matrix.cu:752-759), which is NOT MDS: some survivor sets are singular (12 of
+ * the 1001 four-erasure sets of RS(10,14)).  RSGPU_GEN_CAUCHY builds [I ; C], C[i][j] = 1/((k+i) + j):
+ * every set of k fragments decodes (needs k + p <= 256).  No counterpart in the reference (its
+ * north_star names "Vandermonde/Cauchy generator construction"); fragments made with it decode through
+ * this engine via the matrix stored in METADATA, not through the reference's CPU program, which always
+ * regenerates the Vandermonde matrix (src/cpu-rs.c:616-621).
+ */
+#define RSGPU_GEN_VANDERMONDE 0
+#define RSGPU_GEN_CAUCHY      1
+int rsgpu_create_generator(rsgpu_ctx **out, int device, int k, int p, int generator);
+
 void rsgpu_destroy(rsgpu_ctx *ctx);
 
 int rsgpu_k(const rsgpu_ctx *ctx);
@@ -115,6 +128,18 @@ int rsgpu_decode(rsgpu_ctx *ctx, const uint8_t *survivors_d, size_t survivors_pi
  */
 int rsgpu_decode_erased(rsgpu_ctx *ctx, const uint8_t *survivors_d, size_t survivors_pitch,
                         uint8_t *out_d, size_t out_pitch, size_t len, void *stream);
+
+/*
+ * Repair: rebuild ANY fragments, natives or parities, from k survivors in one multiply.
+ * survivors: k fragment indices in the order of the rows of survivors_d; wanted: n_wanted indices in
+ * [0, k+p).  Output row t of rsgpu_repair is fragment wanted[t].  The e.g. "one storage node lost a
+ * parity fragment" case costs (k + 1)*len bytes of traffic instead of a full decode plus a re-encode.
+ * The reference can only rebuild all k natives (decode_chunk, src/matrix.cu:838-905) and re-encode.
+ * rsgpu_set_repair blocks (it runs the inversion) and may return RSGPU_ESINGULAR.
+ */
+int rsgpu_set_repair(rsgpu_ctx *ctx, const int *survivors /* k */, const int *wanted, int n_wanted);
+int rsgpu_repair(rsgpu_ctx *ctx, const uint8_t *survivors_d, size_t survivors_pitch,
+                 uint8_t *out_d, size_t out_pitch, size_t len, void *stream);
 
 /*
  * Stand-alone GF(2^8) matrix inverse on the GPU, host in / host out (n <= 255).

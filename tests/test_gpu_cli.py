@@ -188,3 +188,18 @@ def test_cli_decode_golden(rs_bin, tmp_path, di):
     if case["reference_correct"]:                  # ... which is what the reference wrote wherever it is right
         import hashlib
         assert hashlib.sha256(got).hexdigest() == case["output_sha256"]
+
+
+def test_cli_cauchy_generator_decodes_reference_singular_set(rs_bin, tmp_path):
+    """RS_GENERATOR=cauchy: the matrix travels in METADATA; a survivor set that is singular under the
+    reference's Vandermonde rows decodes."""
+    data = splitmix64_bytes(8, 123_457)
+    (tmp_path / "f.bin").write_bytes(data.tobytes())
+    env = dict(os.environ, RS_GENERATOR="cauchy")
+    r = subprocess.run([rs_bin, "-k", "10", "-n", "14", "-e", "f.bin"], cwd=tmp_path, env=env, stdout=subprocess.PIPE, text=True)
+    assert r.returncode == 0
+    rows = (tmp_path / "f.bin.METADATA").read_text().splitlines()
+    assert rows[1] == "4 10" and len(rows) == 2 + 14 and rows[12].split()[0] != "1"      # not the all-ones Vandermonde row
+    write_conf(tmp_path, "f.bin", [i for i in range(14) if i not in (0, 1, 2, 12)])
+    run([rs_bin, "-d", "-i", "f.bin", "-c", "conf", "-o", "out.bin"], tmp_path)
+    assert (tmp_path / "out.bin").read_bytes() == data.tobytes()

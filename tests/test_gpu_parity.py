@@ -420,3 +420,50 @@ def test_sampled_windows_vs_oracle_large(rs, orc, torch):
     for s in starts:
         win = a[:, s:s + 4096].cpu().numpy()
         assert (out[:, s:s + 4096].cpu().numpy() == orc.matrix_mul(V, win)).all(), s
+
+
+# ---- repair of arbitrary fragments, Cauchy generator ---------------------------
+
+@pytest.mark.parametrize("k,p,lost", [(10, 4, [3, 12]), (10, 4, [0, 1, 10, 13]), (4, 2, [5]), (16, 4, [2, 7, 16, 19]),
+                                      (32, 8, [0, 5, 33, 39, 31, 32, 34, 1])])
+def test_repair_any_fragments_vs_oracle(rs, orc, torch, k, p, lost):
+    L = 40_000 + 16
+    data = splitmix64_bytes(900 + k, k * L).reshape(k, L)
+    frags = np.concatenate([data, orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)], axis=0)
+    survivors = [i for i in range(k + p) if i not in lost][:k]
+    with rs.RSContext(k, p) as ctx:
+        ctx.set_repair(survivors, lost)
+        d_s = to_dev(torch, frags[survivors])
+        out = torch.empty((len(lost), L), dtype=torch.uint8, device="cuda")
+        ctx.repair(d_s, L, out, L, L, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        assert (out.cpu().numpy() == frags[lost]).all()
+        with pytest.raises(rs.RSGPUError):
+            ctx.set_repair(survivors, [k + p])
+
+
+def test_cauchy_generator_is_mds_and_roundtrips(rs, orc, torch):
+    import itertools
+    k, p, L = 10, 4, 4096 + 32
+    data = splitmix64_bytes(1234, k * L).reshape(k, L)
+    with rs.RSContext(k, p, generator="cauchy") as ctx:
+        T = ctx.total_matrix()
+        assert (T[:k] == np.eye(k, dtype=np.uint8)).all()
+        for i in range(p):
+            for j in range(k):
+                assert orc.gf_mul(int(T[k + i, j]), (k + i) ^ j) == 1          # C[i][j] = 1 / ((k+i) + j)
+        parity = gpu_encode(torch, ctx, data)
+        assert (parity == orc.matrix_mul(T[k:], data)).all()
+        frags = np.concatenate([data, parity], axis=0)
+        # the sets that are singular under the reference's Vandermonde rows decode here,
+        # and so does every other 4-erasure set (sampled) -- the code is MDS
+        sets = [(0, 1, 2, 12), (0, 3, 4, 12), (4, 5, 9, 11)] + list(itertools.combinations(range(14), 4))[::37]
+        for erased in sets:
+            surv = [i for i in range(k + p) if i not in erased]
+            ctx.set_survivors(surv)
+            out = torch.empty((k, L), dtype=torch.uint8, device="cuda")
+            ctx.decode(to_dev(torch, frags[surv]), L, out, L, L)
+            torch.cuda.synchronize()
+            assert (out.cpu().numpy() == data).all(), erased
+    with pytest.raises(rs.RSGPUError):
+        rs.RSContext(250, 10, generator="cauchy")          # k + p > 256
