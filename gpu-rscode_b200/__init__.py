@@ -16,7 +16,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librsgpu.so")
+LIB_PATH = os.environ.get("RSGPU_LIB") or os.path.join(HERE, "librsgpu.so")   # RSGPU_LIB: A/B builds (developer)
 HOST_LIB_PATH = os.path.join(HERE, "librs_host.so")
 RS_BIN = os.path.join(HERE, "RS")
 

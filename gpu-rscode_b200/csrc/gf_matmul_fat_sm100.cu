@@ -25,7 +25,7 @@
 namespace rsgpu {
 namespace {
 
-constexpr int kSmemBudget = 232448 - 512;   // 227 KiB opt-in limit minus alignment slack
+constexpr int kSmemBudget = 232448 - 256 - 1024 - 64;   // 227 KiB opt-in limit minus alignment slack and the two bit-7 constant areas (32 B per fragment, k <= 32)
 
 __host__ __device__ constexpr int fat_count(int k)
 {
@@ -41,9 +41,10 @@ __host__ __device__ constexpr int fat8_count(int k)
     int n8 = left / 16384;
     return n8 > n ? n : n8;
 }
-__host__ __device__ constexpr int fat_threads(int W, int JB)
+__host__ __device__ constexpr int fat_threads(int W, int JB, bool T7)
 {
-    // register budget: accumulators (16 or 32) + two batches of JB vectors
+    // register budget: accumulators (16 or 32, +16 with transposed bit-7 terms) + two batches of JB vectors
+    if (W == 4 && T7) return JB <= 2 ? 768 : (JB <= 4 ? 640 : 512);
     if (W == 4) return JB <= 2 ? 1024 : (JB <= 4 ? 768 : (JB <= 5 ? 640 : 512));
     return JB <= 2 ? 768 : (JB <= 5 ? 512 : 384);
 }
@@ -83,27 +84,31 @@ template <int OFF> __device__ __forceinline__ uint32_t lds32_pinned(uint32_t add
 }
 
 template <int W> struct Acc;
-template <> struct Acc<4> { uint32_t a[16]; };
+// t: bit-7 terms of the fat7 fragments, kept TRANSPOSED (t[4*row + word]: four byte positions of one output
+// row per register, i.e. already in store order) -- see mac_vec
+template <> struct Acc<4> { uint32_t a[16]; uint32_t t[16]; };
 template <> struct Acc<8> { uint32_t a[16]; uint32_t b[16]; };
 
 // Shared-memory map for a K-fragment code (all offsets relative to the 256-aligned base tb):
 //   fragments [0, N8)        fat8 tables, 32 KiB each
 //   fragments [N8, NF)       fat7 tables, 16 KiB each
 //   fragments [NF, K)        split-nibble pages, 256 B each
-//   then K * 8 bytes: the product of 0x80 with every coefficient (bit-7 term of the fat7 fragments)
+//   then K * 16 bytes: the product of 0x80 with every coefficient (bit-7 term of the fat7 fragments)
 template <int K> struct Map {
     static constexpr int NF = fat_count(K);
     static constexpr int N8 = fat8_count(K);
     static constexpr int THIN0 = N8 * 32768 + (NF - N8) * 16384;
     static constexpr int C7 = THIN0 + (K - NF) * 256;
-    static constexpr int BYTES = C7 + K * 8;
+    static constexpr int C7R = C7 + K * 16;    // the same products, one output row per word, byte-replicated
+    static constexpr int BYTES = C7R + K * 16;
+    static_assert(BYTES + 256 <= 232448, "shared-memory plan exceeds the 227 KiB opt-in limit");
     __host__ __device__ static constexpr int off(int j)
     {
         return j < N8 ? j * 32768 : (j < NF ? N8 * 32768 + (j - N8) * 16384 : THIN0 + (j - NF) * 256);
     }
 };
 
-template <int W, int K, int J>
+template <int W, int K, int J, bool T7>
 __device__ __forceinline__ void mac_word(uint32_t w, uint32_t lane_base, uint32_t tb, uint32_t c7a, uint32_t c7b,
                                          Acc<W> &acc, int pos0)
 {
@@ -123,7 +128,7 @@ __device__ __forceinline__ void mac_word(uint32_t w, uint32_t lane_base, uint32_
                 va = v.x;
                 vb = v.y;
             }
-            if constexpr (F7) {
+            if constexpr (F7 && !T7) {
                 // PRMT with the sign-replicate flag (selector nibble 8|b): 0xFFFFFFFF if bit 7 of byte b
                 // is set, else 0.  Raw PTX: the __byte_perm intrinsic drops bit 3 of the selector nibbles.
                 uint32_t m;
@@ -155,33 +160,52 @@ __device__ __forceinline__ void mac_word(uint32_t w, uint32_t lane_base, uint32_
     }
 }
 
-template <int W, int K, int J>
+template <int W, int K, int J, bool T7>
 __device__ __forceinline__ void mac_vec(const uint4 &d, uint32_t lane_base, uint32_t tb, Acc<W> &acc)
 {
     using M = Map<K>;
     uint32_t c7a = 0, c7b = 0;
-    if constexpr (J >= M::N8 && J < M::NF) {   // fat7: the bit-7 term, one broadcast load per 16 bytes
-        c7a = lds32_pinned<M::C7 + J * 8>(tb);
-        if constexpr (W == 8) c7b = lds32_pinned<M::C7 + J * 8 + 4>(tb);
+    if constexpr (J >= M::N8 && J < M::NF) {   // fat7: the bit-7 term
+        if constexpr (!T7) {
+            c7a = lds32_pinned<M::C7 + J * 16>(tb);
+            if constexpr (W == 8) c7b = lds32_pinned<M::C7 + J * 16 + 4>(tb);
+        } else {
+            // Four output rows: instead of (mask, AND, XOR) per BYTE, work per WORD on transposed
+            // accumulators.  One PRMT turns the word into four 0x00/0xFF sign bytes; row r then needs
+            // t[r][word] ^= signs & (product of 0x80 with coefficient r, replicated in all four bytes):
+            // 5 instructions per 4 input bytes instead of 12, and t is already in store order.
+            const uint32_t cr0 = lds32_pinned<M::C7R + J * 16>(tb), cr1 = lds32_pinned<M::C7R + J * 16 + 4>(tb);
+            const uint32_t cr2 = lds32_pinned<M::C7R + J * 16 + 8>(tb), cr3 = lds32_pinned<M::C7R + J * 16 + 12>(tb);
+            const uint32_t ws[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+            for (int wi = 0; wi < 4; ++wi) {
+                uint32_t sg;
+                asm("prmt.b32 %0, %1, %2, %3;" : "=r"(sg) : "r"(ws[wi]), "r"(0u), "r"(0xBA98u));
+                acc.t[wi] ^= sg & cr0;
+                acc.t[4 + wi] ^= sg & cr1;
+                acc.t[8 + wi] ^= sg & cr2;
+                acc.t[12 + wi] ^= sg & cr3;
+            }
+        }
     }
-    mac_word<W, K, J>(d.x, lane_base, tb, c7a, c7b, acc, 0);
-    mac_word<W, K, J>(d.y, lane_base, tb, c7a, c7b, acc, 4);
-    mac_word<W, K, J>(d.z, lane_base, tb, c7a, c7b, acc, 8);
-    mac_word<W, K, J>(d.w, lane_base, tb, c7a, c7b, acc, 12);
+    mac_word<W, K, J, T7>(d.x, lane_base, tb, c7a, c7b, acc, 0);
+    mac_word<W, K, J, T7>(d.y, lane_base, tb, c7a, c7b, acc, 4);
+    mac_word<W, K, J, T7>(d.z, lane_base, tb, c7a, c7b, acc, 8);
+    mac_word<W, K, J, T7>(d.w, lane_base, tb, c7a, c7b, acc, 12);
 }
 
 // compile-time loop over the fragments of batch B
-template <int W, int K, int JB, int B, int JJ>
+template <int W, int K, int JB, int B, int JJ, bool T7>
 struct BatchMac {
     __device__ __forceinline__ static void run(const uint4 (&d)[JB], uint32_t lane_base, uint32_t tb, Acc<W> &acc)
     {
-        mac_vec<W, K, B * JB + JJ>(d[JJ], lane_base, tb, acc);
-        if constexpr (JJ + 1 < JB) BatchMac<W, K, JB, B, JJ + 1>::run(d, lane_base, tb, acc);
+        mac_vec<W, K, B * JB + JJ, T7>(d[JJ], lane_base, tb, acc);
+        if constexpr (JJ + 1 < JB) BatchMac<W, K, JB, B, JJ + 1, T7>::run(d, lane_base, tb, acc);
     }
 };
 
 __device__ __forceinline__ void transpose_store(const uint32_t *a, uint8_t *out, size_t out_pitch, size_t off,
-                                                int row0, int nrows)
+                                                int row0, int nrows, const uint32_t *t = nullptr)
 {
     uint32_t r[4][4];
 #pragma unroll
@@ -193,6 +217,12 @@ __device__ __forceinline__ void transpose_store(const uint32_t *a, uint8_t *out,
         r[1][q] = __byte_perm(t0, t1, 0x7632);
         r[2][q] = __byte_perm(t2, t3, 0x5410);
         r[3][q] = __byte_perm(t2, t3, 0x7632);
+        if (t) {   // compile-time known after inlining: the transposed bit-7 terms
+            r[0][q] ^= t[q];
+            r[1][q] ^= t[4 + q];
+            r[2][q] ^= t[8 + q];
+            r[3][q] ^= t[12 + q];
+        }
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -220,7 +250,7 @@ __device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *&q, si
 // buffers alternate per batch ("ping-pong"): the loads of batch t+1 go into the buffer batch t-1 has just
 // released and are issued BEFORE batch t is consumed, so they have a whole batch of work to land and no
 // register-to-register copies are needed.  SP = which buffer holds batch 0 of this column.
-template <int W, int K, int JB, int KB, int B, int SP, bool PF>
+template <int W, int K, int JB, int KB, int B, int SP, bool PF, bool T7>
 struct ColumnBatches {
     __device__ __forceinline__ static void run(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
                                                const uint8_t *in, size_t vn, size_t nvec, uint32_t lane_base,
@@ -237,13 +267,13 @@ struct ColumnBatches {
                 load_batch<JB, PF>(nxt, q, in_pitch, pf1);
             }
         }
-        BatchMac<W, K, JB, B, 0>::run(cur, lane_base, tb, acc);
+        BatchMac<W, K, JB, B, 0, T7>::run(cur, lane_base, tb, acc);
         if constexpr (B + 1 < KB)
-            ColumnBatches<W, K, JB, KB, B + 1, SP, PF>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1);
+            ColumnBatches<W, K, JB, KB, B + 1, SP, PF, T7>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1);
     }
 };
 
-template <int W, int K, int JB, int KB, int SP, bool PF>
+template <int W, int K, int JB, int KB, int SP, bool PF, bool T7>
 __device__ __forceinline__ void do_column(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
                                           const uint8_t *in, uint8_t *out, size_t out_pitch, size_t v, size_t vn,
                                           size_t nvec, uint32_t lane_base, uint32_t tb, int nrows, uint32_t pf_stride)
@@ -256,14 +286,19 @@ __device__ __forceinline__ void do_column(uint4 (&buf0)[JB], uint4 (&buf1)[JB], 
     for (int i = 0; i < 16; ++i) {
         acc.a[i] = 0;
         if constexpr (W == 8) acc.b[i] = 0;
+        else if constexpr (T7) acc.t[i] = 0;
     }
-    ColumnBatches<W, K, JB, KB, 0, SP, PF>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1);
-    transpose_store(acc.a, out, out_pitch, v * 16, 0, nrows);
-    if constexpr (W == 8) transpose_store(acc.b, out, out_pitch, v * 16, 4, nrows - 4);
+    ColumnBatches<W, K, JB, KB, 0, SP, PF, T7>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1);
+    if constexpr (W == 8) {
+        transpose_store(acc.a, out, out_pitch, v * 16, 0, nrows);
+        transpose_store(acc.b, out, out_pitch, v * 16, 4, nrows - 4);
+    } else {
+        transpose_store(acc.a, out, out_pitch, v * 16, 0, nrows, (T7 && Map<K>::NF > Map<K>::N8) ? acc.t : nullptr);
+    }
 }
 
-template <int W, int JB, int KB, bool PF>
-__global__ void __launch_bounds__(fat_threads(W, JB), 1)
+template <int W, int JB, int KB, bool PF, bool T7>
+__global__ void __launch_bounds__(fat_threads(W, JB, T7), 1)
 k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
                 const uint32_t *__restrict__ tab, int nrows, size_t nvec)
 {
@@ -310,10 +345,13 @@ k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__rest
         const uint32_t v = __ldg(tab + (size_t)(M::NF + j) * 32 * WW + r);
         asm volatile("st.shared.u32 [%0], %1;" ::"r"(tb + M::THIN0 + j * 256 + r * 4), "r"(v) : "memory");
     }
-    for (int i = tid; i < K * 2; i += nt) {                   // product of 0x80 = hi-table entry 8
-        const int j = i >> 1, q = i & 1;
-        const uint32_t v = q < WW ? __ldg(tab + (size_t)j * 32 * WW + (16 + 8) * WW + q) : 0u;
-        asm volatile("st.shared.u32 [%0], %1;" ::"r"(tb + M::C7 + i * 4), "r"(v) : "memory");
+    for (int i = tid; i < K * 4; i += nt) {                   // product of 0x80 = hi-table entry 8
+        const int j = i >> 2, q = i & 3;
+        const uint32_t packed = q < WW ? __ldg(tab + (size_t)j * 32 * WW + (16 + 8) * WW + q) : 0u;
+        const uint32_t c = __ldg(tab + (size_t)j * 32 * WW + (16 + 8) * WW);
+        const uint32_t repl = ((c >> (8 * q)) & 0xFFu) * 0x01010101u;   // rows 0..3, one per word
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(tb + M::C7 + i * 4), "r"(packed) : "memory");
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(tb + M::C7R + i * 4), "r"(repl) : "memory");
     }
     __syncthreads();
 
@@ -327,11 +365,11 @@ k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__rest
     if (v < nvec) load_batch<JB, PF>(buf0, q, in_pitch, v + stride < nvec ? pf_stride : 0u);
 
     while (v < nvec) {
-        do_column<W, K, JB, KB, 0, PF>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride);
+        do_column<W, K, JB, KB, 0, PF, T7>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride);
         v += stride;
         if constexpr (KB & 1) {          // odd batch count: the next column starts in the other buffer
             if (v >= nvec) break;
-            do_column<W, K, JB, KB, 1, PF>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride);
+            do_column<W, K, JB, KB, 1, PF, T7>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride);
             v += stride;
         }
     }
@@ -352,7 +390,13 @@ FatKernel make_fat()
     // HBM peak): RS(8,12) 0.894 -> 0.934, RS(10,14) 0.896 -> 0.991, RS(12,16) 0.866 -> 0.913, RS(14,18) 0.796 ->
     // 0.893, RS(16,20) 0.885 -> 0.928, RS(20,24) 0.824 -> 0.858; but RS(6,9) 0.970 -> 0.906, RS(4,6) 0.99 -> 0.87.
     constexpr bool PF = (JB * KB >= 8);
-    return FatKernel{k_gf_matmul_fat<W, JB, KB, PF>, fat_threads(W, JB), Map<JB * KB>::BYTES + 256};
+    // transposed bit-7 accumulation (mac_vec): fewer alu instructions, 16 more registers.  It pays for the
+    // fat7-heavy shapes with an even batch count (same box, off -> on: RS(14,18) 0.888 -> 0.945, RS(16,20)
+    // 0.874 -> 0.915, RS(20,24) 0.848 -> 0.863) and loses where the extra registers spill or cost threads
+    // (RS(10,14) 0.930 -> 0.754, RS(12,16) 0.878 -> 0.639).
+    constexpr int K = JB * KB;
+    constexpr bool T7 = (W == 4) && (K == 14 || K == 16 || K == 20);
+    return FatKernel{k_gf_matmul_fat<W, JB, KB, PF, T7>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
 }
 
 // Batch shape per k (JB fragments per batch x KB batches), measured on B200: batches of 4 with 768
