@@ -233,7 +233,7 @@ def main():
     rs.lib()
 
     torch.cuda.set_device(local_rank)
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    sampler = ClockSampler(local_rank) if (rank == 0 and not os.environ.get('BENCH_NO_SMI')) else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n_gpus = world

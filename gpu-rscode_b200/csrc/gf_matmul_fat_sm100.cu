@@ -395,13 +395,15 @@ FatKernel make_fat()
     // 0.874 -> 0.915, RS(20,24) 0.848 -> 0.863) and loses where the extra registers spill or cost threads
     // (RS(10,14) 0.930 -> 0.754, RS(12,16) 0.878 -> 0.639).
     constexpr int K = JB * KB;
-    constexpr bool T7 = (W == 4) && (K == 14 || K == 16 || K == 20);
+    constexpr bool T7 = (W == 4) && (K == 12 || K == 14 || K == 16 || K == 18 || K == 20);
     return FatKernel{k_gf_matmul_fat<W, JB, KB, PF, T7>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
 }
 
 // Batch shape per k (JB fragments per batch x KB batches), measured on B200: batches of 4 with 768
 // threads beat batches of 8 with 512 (RS(16,20): 0.888 vs 0.794 of the HBM peak, RS(8,12): 0.898 vs 0.816);
-// RS(10,14): batches of 2 with 1024 threads 0.900, batches of 5 with 640 threads 0.869.
+// An even batch count matters more than the batch size: an odd one makes the two register buffers swap
+// roles per column, the loop is unrolled over two columns and spills (same box, with the L2 prefetch:
+// RS(10,14) 2x5 0.944 vs 5x2 1.005; RS(12,16) 4x3 0.890 vs 3x4 0.989 of the measured copy peak).
 template <int W>
 bool pick_fat(int k, FatKernel *fk)
 {
@@ -414,8 +416,8 @@ bool pick_fat(int k, FatKernel *fk)
     case 15: *fk = make_fat<W, 5, 3>(); return true;
     case 18: *fk = make_fat<W, 3, 6>(); return true;
     case 8: *fk = make_fat<W, 4, 2>(); return true;
-    case 10: *fk = make_fat<W, 2, 5>(); return true;
-    case 12: *fk = make_fat<W, 4, 3>(); return true;
+    case 10: *fk = make_fat<W, 5, 2>(); return true;
+    case 12: *fk = make_fat<W, 3, 4>(); return true;
     case 14: *fk = make_fat<W, 7, 2>(); return true;
     case 16: *fk = make_fat<W, 4, 4>(); return true;
     case 20: *fk = make_fat<W, 5, 4>(); return true;
