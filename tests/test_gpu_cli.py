@@ -203,3 +203,24 @@ def test_cli_cauchy_generator_decodes_reference_singular_set(rs_bin, tmp_path):
     write_conf(tmp_path, "f.bin", [i for i in range(14) if i not in (0, 1, 2, 12)])
     run([rs_bin, "-d", "-i", "f.bin", "-c", "conf", "-o", "out.bin"], tmp_path)
     assert (tmp_path / "out.bin").read_bytes() == data.tobytes()
+
+
+def test_cli_streaming_many_slabs_ring_reuse(rs_bin, tmp_path):
+    """A file big enough that the slab ring (GPUs + 2 slots) is reused many times: RS(32,40), 230 MB ->
+    chunk 7.2 MB, 2 MiB slabs."""
+    import hashlib
+    size = 230_000_003
+    data = splitmix64_bytes(0xC5, size)
+    (tmp_path / "big.bin").write_bytes(data.tobytes())
+    want = hashlib.sha256(data.tobytes()).hexdigest()
+    del data
+    run([rs_bin, "-k", "32", "-n", "40", "-e", "big.bin"], tmp_path)
+    assert (tmp_path / "_39_big.bin").stat().st_size == (size + 31) // 32
+    order = list(range(32, 40)) + list(range(8, 32))
+    write_conf(tmp_path, "big.bin", order)
+    run([rs_bin, "-d", "-i", "big.bin", "-c", "conf", "-o", "out.bin"], tmp_path)
+    h = hashlib.sha256()
+    with open(tmp_path / "out.bin", "rb") as f:
+        for blk in iter(lambda: f.read(1 << 24), b""):
+            h.update(blk)
+    assert h.hexdigest() == want

@@ -467,3 +467,23 @@ def test_cauchy_generator_is_mds_and_roundtrips(rs, orc, torch):
             assert (out.cpu().numpy() == data).all(), erased
     with pytest.raises(rs.RSGPUError):
         rs.RSContext(250, 10, generator="cauchy")          # k + p > 256
+
+
+# ---- randomized shapes (hypothesis): any k, p, length, pitch, misalignment, kernel variant -----------
+
+def test_fuzz_encode_shapes_vs_oracle(rs, orc, torch):
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=60, deadline=None, derandomize=True, suppress_health_check=list(HealthCheck))
+    @given(k=st.integers(1, 40), p=st.integers(1, 12), L=st.integers(1, 70_000), pad=st.sampled_from([0, 0, 16, 48, 5]),
+           in_off=st.sampled_from([0, 0, 16, 3]), out_off=st.sampled_from([0, 0, 32, 7]),
+           variant=st.sampled_from([0, 1, 5, 6, 7]), seed=st.integers(0, 2**31))
+    def run(k, p, L, pad, in_off, out_off, variant, seed):
+        data = np.random.default_rng(seed).integers(0, 256, (k, L), dtype=np.uint8)
+        pitch = (L + 15) // 16 * 16 + pad
+        with rs.RSContext(k, p) as ctx:
+            ctx.set_tuning(variant=variant)
+            got = gpu_encode(torch, ctx, data, pitch=pitch, out_pitch=pitch + 16, in_off=in_off, out_off=out_off)
+        assert (got == orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)).all(), (k, p, L, pad, in_off, out_off, variant)
+
+    run()

@@ -31,13 +31,12 @@ __global__ void pat(const unsigned char *in, size_t pitch, unsigned char *out, s
     }
 }
 template <int K, int P, int DEPTH>
-void run(const char *name, size_t L, int threads, int blocks, int blockmajor) {
+void run(const char *name, size_t L, int threads, int blocks, int blockmajor, int reps = 10) {
     unsigned char *in, *out; cudaMalloc(&in, (size_t)K * L); cudaMalloc(&out, (size_t)P * L);
     cudaMemset(in, 1, (size_t)K * L);
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     for (int i = 0; i < 3; ++i) pat<K, P, DEPTH><<<blocks, threads>>>(in, L, out, L, L / 16, blockmajor);
     cudaEventRecord(e0);
-    const int reps = 10;
     for (int i = 0; i < reps; ++i) pat<K, P, DEPTH><<<blocks, threads>>>(in, L, out, L, L / 16, blockmajor);
     cudaEventRecord(e1); cudaEventSynchronize(e1);
     float ms; cudaEventElapsedTime(&ms, e0, e1); ms /= reps;
@@ -46,7 +45,11 @@ void run(const char *name, size_t L, int threads, int blocks, int blockmajor) {
            (double)(K + P) * L / ms / 1e6, e == cudaSuccess ? "" : cudaGetErrorString(e));
     cudaFree(in); cudaFree(out);
 }
-int main() {
+int main(int argc, char **argv) {
+    if (argc > 1) {   // sustained mode: ./membench <reps>  -- only the RS(10,14) pattern, for power readings
+        run<10, 4, 1>("rs1014", (size_t)400 << 20, 768, 148, 0, atoi(argv[1]));
+        return 0;
+    }
     size_t L10 = (size_t)400 << 20, L4 = (size_t)512 << 20, L16 = (size_t)256 << 20;
     for (int bm = 0; bm < 2; ++bm) {
         run<4, 2, 1>("rs46", L4, 768, 148, bm);
