@@ -66,7 +66,7 @@ typedef struct {
     int n_dst;
     int grid_cap;                /* reference -p, 0 = default */
     int slots;                   /* reference -s, <= 0 = default */
-    int io_threads;              /* <= 0 = default (8) */
+    int io_threads;              /* <= 0 = RS_IO_THREADS, else the online cores clamped to 4..16 */
     int max_gpus;                /* <= 0 = every visible GPU */
 } rs_stream_desc;
 
