@@ -232,6 +232,8 @@ def main():
         raise SystemExit("bench.py needs a CUDA device (the product path has no CPU fallback)")
     rs = importlib.import_module("gpu-rscode_b200")
     sharding = importlib.import_module("gpu-rscode_b200.sharding")
+    if not os.path.exists(rs.LIB_PATH) and local_rank == 0:
+        rs.build()          # fresh checkout: compile in-tree (nvcc, sm_100a); there is no other path
     rs.lib()
 
     torch.cuda.set_device(local_rank)
