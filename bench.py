@@ -144,7 +144,7 @@ def run_reference_arm(args, rank):
     val = b_total / t_total / 1e9
     line = {
         "impl": "reference",
-        "metric": "RS(%d,%d) %s throughput, input bytes" % (k, k + p, mode),
+        "metric": "%s GB/s (input bytes) RS(%d,%d)" % (mode, k, k + p),
         "value": val, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t_total / max(1, args.steps), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
@@ -338,18 +338,19 @@ def main():
     elapsed_ms = float(t.item())
     value = sharding.job_throughput_gbs(k * L, n_gpus, args.steps, elapsed_ms)
 
-    # ---- correctness spot check of what was just timed (oracle on a 64 KiB window) ----
+    # ---- sanity check of what was just timed, by size-independent properties on the FULL buffers (no
+    # oracle here: oracle/ is only used by the cpu_baseline leg): row 0 of the generator is all ones, so
+    # parity 0 must be the XOR of the k fragments; a decode must return the erased natives ----
     check = "skipped"
     if rank == 0:
-        from oracle_lib import Oracle
-        orc = Oracle()
-        w0 = (L // 2) // 16 * 16
-        win = slice(w0, w0 + 65536)
         if mode == "encode":
-            want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), data[:, win].cpu().numpy())
+            x = data[0].clone()
+            for j in range(1, k):
+                x ^= data[j]
+            check = "ok" if bool((out[0] == x).all()) else "MISMATCH"
+            del x
         else:
-            want = data[:rows_out, win].cpu().numpy()
-        check = "ok" if (out[:, win].cpu().numpy() == want).all() else "MISMATCH"
+            check = "ok" if bool((out == data[:rows_out]).all()) else "MISMATCH"
 
     # ---- end to end through the host-buffer C-ABI call ----
     e2e = None
@@ -396,11 +397,8 @@ def main():
                "h2d_bytes_per_step": k * e2e_L, "d2h_bytes_per_step": rows_out * e2e_L,
                "steps": e2e_steps, "fragment_bytes": e2e_L,
                "api": "%s (pinned host buffers, H2D+kernel+D2H pipelined inside the call)%s" % ("rsgpu_encode_host" if mode == "encode" else "rsgpu_set_survivors + rsgpu_decode_erased_host", note)}
-        if rank == 0 and mode == "encode":
-            from oracle_lib import Oracle
-            orc = Oracle()
-            want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), h_in[:, :65536].numpy())
-            if not (h_out[:, :65536].numpy() == want).all():
+        if rank == 0:   # the host-path result must equal the device-path result of the same input
+            if not bool((h_out.cuda(dev) == out[:, :e2e_L]).all()):
                 check = "MISMATCH(e2e)"
         del h_in, h_out
 
@@ -446,14 +444,14 @@ def main():
                "value_1core": v1, "sample_1core": "%d MiB input, %.1f s" % (nb1 // MIB, dt1)}
 
     line = {
-        "metric": "RS(%d,%d) %s throughput, input bytes" % (k, k + p, mode),
+        "metric": "%s GB/s (input bytes) RS(%d,%d)" % (mode, k, k + p),
         "value": value, "unit": "GB/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": desc, "k": k, "p": p, "fragment_bytes": L, "input_bytes_per_gpu_per_step": k * L,
                    "l2_policy": "inputs (%.1f GB) larger than L2, no flush" % (k * L / 1e9),
                    "parallelism": "stripes sharded across %d GPU(s), no collective on the data path" % n_gpus,
-                   "variant": args.variant, "check_vs_oracle": check},
+                   "variant": args.variant, "self_check": check},
         "roofline": roofline,
         "cpu_baseline": cpu,
         "e2e": e2e,
