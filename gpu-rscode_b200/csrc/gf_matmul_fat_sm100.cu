@@ -11,10 +11,10 @@
 // input fragment ("fat8"), or 16 KiB if bit 7 of the byte is peeled off and handled in registers
 // ("fat7": index = low 7 bits, plus (sign mask & product-of-0x80) from one PRMT and one LOP3).
 // With 227 KiB per SM a block holds e.g. 4 fat8 + 6 fat7 tables for k = 10, or 14 fat7 + 2 nibble pages
-// for k = 16; fragments that do not fit keep the split-nibble tables.  One block of 512-768 threads per
+// for k = 16; fragments that do not fit keep the split-nibble tables.  One block of 384-768 threads per
 // SM builds the replicated tables once (from the same 32-entry global tables the other kernel uses) and
-// then streams columns exactly like the first kernel: 128-bit loads, register double buffering, XOR
-// accumulate, PRMT transpose, 128-bit stores.
+// then streams columns like the first kernel: 128-bit loads into two ping-pong register buffers (plus an
+// L2 prefetch one grid stride ahead), XOR accumulate, PRMT transpose, 128-bit stores.
 //
 // Index arithmetic: address = lane_base + x * 128.  __dp4a(w, 0x80 << 8b, lane_base) selects byte b of
 // the data word, scales it by 128 and adds the lane base in ONE fmaheavy-pipe instruction, no mask, no
