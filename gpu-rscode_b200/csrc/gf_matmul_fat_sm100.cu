@@ -439,7 +439,8 @@ cudaError_t launch_matmul_fat(const RowGroup &g, int k, const uint8_t *in, size_
     const bool ok = g.width == 4 ? pick_fat<4>(k, &fk) : pick_fat<8>(k, &fk);
     if (!ok || fk.smem > dev.max_smem_optin) return cudaErrorNotSupported;
     if (threads > 0 && threads < fk.threads) fk.threads = threads;   // tuning: fewer threads than the launch bound
-    cudaError_t e = cudaFuncSetAttribute((const void *)fk.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, fk.smem);
+    int occ = 0;   // always 1: the tables fill the SM's shared memory; the call raises the opt-in attribute once
+    cudaError_t e = prepare_launch(dev, (const void *)fk.fn, fk.threads, (size_t)fk.smem, &occ);
     if (e != cudaSuccess) return e;
     size_t want = (nvec + fk.threads - 1) / fk.threads;
     size_t cap = (size_t)dev.sm_count;      // one block per SM: the tables fill its shared memory

@@ -171,6 +171,34 @@ int choose_jb(int k)
 
 }  // namespace
 
+cudaError_t prepare_launch(const DeviceInfo &dev, const void *fn, int threads, size_t smem, int *occ)
+{
+    LaunchMemo *m = dev.memo;
+    if (m)
+        for (int i = 0; i < m->n; ++i)
+            if (m->fn[i] == fn && m->threads[i] == threads && m->smem[i] == (int)smem) {
+                *occ = m->occ[i];
+                return cudaSuccess;
+            }
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    int o = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, fn, threads, smem);
+    if (e != cudaSuccess) return e;
+    if (o < 1) o = 1;
+    *occ = o;
+    if (m && m->n < LaunchMemo::kSlots) {
+        m->fn[m->n] = fn;
+        m->threads[m->n] = threads;
+        m->smem[m->n] = (int)smem;
+        m->occ[m->n] = o;
+        ++m->n;
+    }
+    return cudaSuccess;
+}
+
 cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
                                 const uint8_t *in, size_t in_pitch, uint8_t *out, size_t out_pitch,
                                 size_t len, const Tuning &tune, const DeviceInfo &dev,
@@ -214,14 +242,9 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
         // 45 % instead of 81 %, profiles/r1_pipes_variant*.csv); variant 1 selects the PRMT splice
         MatmulFn fn = pick_kernel(g.width, jb, tune.variant == 1, kb * jb > k);
         const size_t smem = (size_t)kpad * 256 + 256;   // one page per fragment + alignment slack
-        if (smem > 48 * 1024) {
-            cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess) return e;
-        }
         int occ = 0;
-        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)fn, threads, smem);
+        cudaError_t e = prepare_launch(dev, (const void *)fn, threads, smem, &occ);
         if (e != cudaSuccess) return e;
-        if (occ < 1) occ = 1;
         size_t want = (nvec + threads - 1) / threads;
         size_t cap = (size_t)dev.sm_count * occ;
         if (tune.max_blocks > 0 && (size_t)tune.max_blocks < cap) cap = tune.max_blocks;

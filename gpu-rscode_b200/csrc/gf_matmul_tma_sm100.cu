@@ -174,12 +174,9 @@ cudaError_t launch_matmul_tma(const RowGroup &g, int k, int kpad, const uint8_t 
     const int nst = jb == 8 ? 3 : 4;
     const size_t smem = 256 + (size_t)kpad * 256 + (size_t)nst * jb * kTileBytes + 2 * nst * 8;
     if ((int)smem > dev.max_smem_optin) return cudaErrorNotSupported;
-    cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
     int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)fn, kTileVec + 32, smem);
+    cudaError_t e = prepare_launch(dev, (const void *)fn, kTileVec + 32, smem, &occ);
     if (e != cudaSuccess) return e;
-    if (occ < 1) occ = 1;
     const size_t ntiles = (nvec + kTileVec - 1) / kTileVec;
     size_t cap = (size_t)dev.sm_count * occ;
     if (max_blocks > 0 && (size_t)max_blocks < cap) cap = max_blocks;

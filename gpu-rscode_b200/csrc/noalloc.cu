@@ -41,6 +41,7 @@ constexpr int kMaxDevices = 64;
 std::mutex g_mu;
 uint8_t *g_scratch_addr[kMaxDevices] = {};
 DeviceInfo g_dev_info[kMaxDevices];
+LaunchMemo g_memo[kMaxDevices];   // host memory, one per device; guarded by the caller's one-call-at-a-time rule
 
 int scratch_for_current_device(uint8_t **addr, DeviceInfo *info)
 {
@@ -60,6 +61,7 @@ int scratch_for_current_device(uint8_t **addr, DeviceInfo *info)
             return fail_cuda(e, "cudaDeviceGetAttribute(MaxSharedMemoryPerBlockOptin)");
         g_dev_info[dev].sm_count = sms;
         g_dev_info[dev].max_smem_optin = smem;
+        g_dev_info[dev].memo = &g_memo[dev];
         g_scratch_addr[dev] = p;
     }
     *addr = g_scratch_addr[dev];

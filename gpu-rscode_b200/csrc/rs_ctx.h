@@ -8,6 +8,7 @@ struct rsgpu_ctx {
     int device = 0;
     int k = 0, p = 0;
     rsgpu::DeviceInfo dev;
+    rsgpu::LaunchMemo memo;       // dev.memo points here
     rsgpu::GfTables gf;
     rsgpu::Tuning tune;
     cudaStream_t setup_stream = nullptr;

@@ -66,10 +66,26 @@ cudaError_t launch_gj_invert(const uint8_t *d_in, uint8_t *d_inv, int n, int *d_
                              const GfTables &gf, cudaStream_t s);
 
 // ---- gf_matmul_sm100.cu ---------------------------------------------------------------------
+// Memo of launch set-up per (kernel, block size, dynamic shared memory): the opt-in shared-memory attribute
+// has been raised and the resident blocks per SM are known, so a repeat launch costs no runtime queries
+// (they are ~3-5 us per call, as much as a whole kernel on a 1 MiB stripe).  One memo per context (= per
+// device and host thread); not thread-safe, like the context.
+struct LaunchMemo {
+    static constexpr int kSlots = 32;
+    const void *fn[kSlots];
+    int threads[kSlots];
+    int smem[kSlots];
+    int occ[kSlots];
+    int n = 0;
+};
+
 struct DeviceInfo {
     int sm_count = 0;
     int max_smem_optin = 0;
+    LaunchMemo *memo = nullptr;   // may be null: then every launch queries
 };
+// Raises cudaFuncAttributeMaxDynamicSharedMemorySize if needed and returns the resident blocks per SM.
+cudaError_t prepare_launch(const DeviceInfo &dev, const void *fn, int threads, size_t smem, int *occ);
 // out rows [g.row0, g.row0+g.nrows) = matrix rows * in, bytes [0, len).  *launches += kernels launched.
 cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
                                 const uint8_t *in, size_t in_pitch, uint8_t *out, size_t out_pitch,

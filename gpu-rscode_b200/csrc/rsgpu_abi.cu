@@ -126,6 +126,7 @@ static int ctx_create(rsgpu_ctx **out, int device, int k, int p, const uint8_t *
     if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return bail(fail_msg(RSGPU_ECUDA, "cudaGetDeviceProperties failed"));
     c->dev.sm_count = prop.multiProcessorCount;
     c->dev.max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+    c->dev.memo = &c->memo;
 
     cudaError_t e;
     if ((e = cudaStreamCreateWithFlags(&c->setup_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(fail_cuda(e, "cudaStreamCreate"));
