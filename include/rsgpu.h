@@ -91,6 +91,9 @@ int rsgpu_get_total_matrix(rsgpu_ctx *ctx, uint8_t *total_matrix);
  * Replaces encode_chunk (src/matrix.h:80, src/matrix.cu:767-830) and both matrix_mul kernels
  * (src/matrix.cu:232-323, 335-407).  Unlike the reference it overwrites parity (no pre-zeroing
  * needed), takes pitches, 64-bit len, and never synchronises.
+ * Byte columns are independent, so a BATCH of stripes stored fragment-major -- row j = fragment j of
+ * stripe 0, then of stripe 1, ... (pitch = stripes * stripe_len) -- is one call with len = stripes *
+ * stripe_len: one launch, tables built once, which is how small stripes reach the large-stripe rate.
  */
 int rsgpu_encode(rsgpu_ctx *ctx, const uint8_t *data_d, size_t data_pitch,
                  uint8_t *parity_d, size_t parity_pitch, size_t len, void *stream);

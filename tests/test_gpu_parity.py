@@ -487,3 +487,15 @@ def test_fuzz_encode_shapes_vs_oracle(rs, orc, torch):
         assert (got == orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)).all(), (k, p, L, pad, in_off, out_off, variant)
 
     run()
+
+
+def test_batch_of_small_stripes_is_one_call(rs, orc, torch):
+    """include/rsgpu.h: stripes stored fragment-major side by side are ONE encode of len = stripes * L."""
+    k, p, L, n = 10, 4, 64 * 1024, 24
+    stripes = [splitmix64_bytes(7000 + s, k * L).reshape(k, L) for s in range(n)]
+    batch = np.concatenate(stripes, axis=1)                      # row j = fragment j of stripe 0, 1, ...
+    with rs.RSContext(k, p) as ctx:
+        got = gpu_encode(torch, ctx, batch)
+    V = orc.gen_encoding_matrix(p, k)
+    for s in (0, 7, n - 1):
+        assert (got[:, s * L:(s + 1) * L] == orc.matrix_mul(V, stripes[s])).all()
