@@ -36,7 +36,7 @@ ABI_SYMBOLS = [
     "rsgpu_invert_matrix", "rsgpu_matmul", "rsgpu_encode_host", "rsgpu_decode_host", "rsgpu_decode_erased_host", "rsgpu_host_alloc",
     "rsgpu_host_free", "rsgpu_host_register", "rsgpu_host_unregister", "rsgpu_dev_alloc", "rsgpu_dev_free",
     "rsgpu_memcpy_h2d", "rsgpu_memcpy_d2h", "rsgpu_sync", "rsgpu_set_tuning", "rsgpu_launch_count",
-    "rsgpu_encode_noalloc", "rsgpu_create_generator", "rsgpu_set_repair", "rsgpu_repair",
+    "rsgpu_encode_noalloc", "rsgpu_create_generator", "rsgpu_set_repair", "rsgpu_repair", "rsgpu_enable_peer", "rsgpu_encode_rows",
 ]
 
 
@@ -78,6 +78,8 @@ def lib():
     L.rsgpu_create_generator.argtypes = [C.POINTER(vp), i32, i32, i32, i32]
     L.rsgpu_set_repair.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), i32]
     L.rsgpu_repair.argtypes = [vp, u8p, sz, u8p, sz, sz, vp]
+    L.rsgpu_enable_peer.argtypes = [vp, i32]
+    L.rsgpu_encode_rows.argtypes = [vp, u8p, sz, C.POINTER(vp), sz, vp]
     L.rsgpu_destroy.argtypes = [vp]
     L.rsgpu_destroy.restype = None
     for f in ("rsgpu_k", "rsgpu_p", "rsgpu_device"):
@@ -220,6 +222,14 @@ class RSContext:
     # -- device-pointer coding ----------------------------------------------------------------
     def encode(self, data_d, data_pitch, parity_d, parity_pitch, length, stream=0):
         _check(lib().rsgpu_encode(self._h, _ptr(data_d), data_pitch, _ptr(parity_d), parity_pitch, length, stream))
+
+    def enable_peer(self, peer_device):
+        _check(lib().rsgpu_enable_peer(self._h, peer_device))
+
+    def encode_rows(self, data_d, data_pitch, parity_rows, length, stream=0):
+        """parity_rows: p device pointers / tensors, each may live on a peer GPU (after enable_peer)."""
+        arr = (C.c_void_p * self.p)(*[_ptr(r) for r in parity_rows])
+        _check(lib().rsgpu_encode_rows(self._h, _ptr(data_d), data_pitch, arr, length, stream))
 
     def decode(self, surv_d, surv_pitch, natives_d, natives_pitch, length, stream=0):
         _check(lib().rsgpu_decode(self._h, _ptr(surv_d), surv_pitch, _ptr(natives_d), natives_pitch, length, stream))

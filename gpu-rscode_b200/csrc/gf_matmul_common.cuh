@@ -133,5 +133,23 @@ __device__ __forceinline__ void transpose_store(const uint32_t *a, uint8_t *out,
             stg_stream(out + (size_t)(row0 + i) * out_pitch + off, make_uint4(r[i][0], r[i][1], r[i][2], r[i][3]));
 }
 
+// Load one batch of JB fragment vectors through a running pointer (q += pitch per fragment: two adds
+// instead of a 64-bit multiply-add chain per load).  PAD: the last batch may run past fragment k-1;
+// padded slots re-read the last valid row (their tables are all zero).
+template <int JB, bool PAD>
+__device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *&q, size_t in_pitch, int &j, int k)
+{
+#pragma unroll
+    for (int jj = 0; jj < JB; ++jj) {
+        d[jj] = ldg_stream(q);
+        if constexpr (PAD) {
+            ++j;
+            if (j < k) q += in_pitch;
+        } else {
+            q += in_pitch;
+        }
+    }
+}
+
 }  // namespace
 }  // namespace rsgpu

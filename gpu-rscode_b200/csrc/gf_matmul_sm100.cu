@@ -27,24 +27,6 @@
 namespace rsgpu {
 namespace {
 
-// Load one batch of JB fragment vectors through a running pointer (q += pitch per fragment: two adds
-// instead of a 64-bit multiply-add chain per load).  PAD: the last batch may run past fragment k-1;
-// padded slots re-read the last valid row (their tables are all zero).
-template <int JB, bool PAD>
-__device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *&q, size_t in_pitch, int &j, int k)
-{
-#pragma unroll
-    for (int jj = 0; jj < JB; ++jj) {
-        d[jj] = ldg_stream(q);
-        if constexpr (PAD) {
-            ++j;
-            if (j < k) q += in_pitch;
-        } else {
-            q += in_pitch;
-        }
-    }
-}
-
 // W: table entry bytes (4: up to 4 output rows, 8: up to 8).  JB: fragments per load batch.
 // kb = number of batches (kb*JB >= k, kb*JB <= kpad); PAD = (kb*JB > k).
 template <int W, int JB, int EX, bool PAD>

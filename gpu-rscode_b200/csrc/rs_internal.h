@@ -101,6 +101,12 @@ cudaError_t launch_matmul_fat(const RowGroup &g, int k, const uint8_t *in, size_
                               cudaStream_t s);
 
 
+// ---- gf_matmul_rows_sm100.cu --------------------------------------------------------------------
+// One destination pointer per output row (rows may be peer-GPU memory: the stores go over NVLink).
+cudaError_t launch_matmul_rows(const RowGroup &g, int k, int kpad, const uint8_t *in, size_t in_pitch,
+                               uint8_t *const *out_rows, size_t len, const DeviceInfo &dev, cudaStream_t s,
+                               long long *launches);
+
 // ---- gf_matmul_tma_sm100.cu ---------------------------------------------------------------------
 // Split-nibble kernel fed by TMA bulk copies through a shared-memory stage ring (tuning variant 7).
 // cudaErrorNotSupported when k has no divisor among the compiled batch sizes.

@@ -257,6 +257,41 @@ int rsgpu_encode(rsgpu_ctx *c, const uint8_t *data_d, size_t data_pitch, uint8_t
     return plan_apply(c, c->enc, data_d, data_pitch, parity_d, parity_pitch, len, (cudaStream_t)stream);
 }
 
+int rsgpu_enable_peer(rsgpu_ctx *c, int peer_device)
+{
+    if (!c) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (peer_device == c->device) return RSGPU_OK;
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    int can = 0;
+    CK(cudaDeviceCanAccessPeer(&can, c->device, peer_device));
+    if (!can) return fail_msg(RSGPU_EINVAL, "this device cannot access the peer's memory");
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) {
+        cudaGetLastError();   // clear the sticky-less error state
+        return RSGPU_OK;
+    }
+    if (e != cudaSuccess) return fail_cuda(e, "cudaDeviceEnablePeerAccess");
+    return RSGPU_OK;
+}
+
+int rsgpu_encode_rows(rsgpu_ctx *c, const uint8_t *data_d, size_t data_pitch, uint8_t *const *parity_rows, size_t len,
+                      void *stream)
+{
+    if (!c || !data_d || !parity_rows) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (c->p == 0) return RSGPU_OK;
+    for (int i = 0; i < c->p; ++i)
+        if (!parity_rows[i]) return fail_msg(RSGPU_EINVAL, "NULL row pointer");
+    if (c->k > 1 && data_pitch < len) return fail_msg(RSGPU_EINVAL, "pitch < len");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    if (len == 0) return RSGPU_OK;
+    for (int g = 0; g < c->enc.ngroups; ++g)
+        CK(launch_matmul_rows(c->enc.grp[g], c->k, c->enc.kpad, data_d, data_pitch, parity_rows, len, c->dev,
+                              (cudaStream_t)stream, &c->launches));
+    return RSGPU_OK;
+}
+
 int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
 {
     if (!c || !idx) return fail_msg(RSGPU_EINVAL, "NULL argument");

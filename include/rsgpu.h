@@ -99,6 +99,18 @@ int rsgpu_encode(rsgpu_ctx *ctx, const uint8_t *data_d, size_t data_pitch,
                  uint8_t *parity_d, size_t parity_pitch, size_t len, void *stream);
 
 /*
+ * Encode with one destination pointer per parity row (host array of p device pointers).  The rows may
+ * be memory of OTHER GPUs of the box once rsgpu_enable_peer(ctx, that_device) has succeeded: the kernel's
+ * 128-bit stores then travel over NVLink / NVSwitch while it computes the following columns, so the
+ * parity fragments arrive on the devices (storage nodes) that keep them without a staging buffer or a
+ * separate copy.  No counterpart in the reference, which gathers every fragment on the host
+ * (src/encode.cu:410-429); SURVEY 8f-3.  Asynchronous on `stream` (a stream of the context's device).
+ */
+int rsgpu_enable_peer(rsgpu_ctx *ctx, int peer_device);
+int rsgpu_encode_rows(rsgpu_ctx *ctx, const uint8_t *data_d, size_t data_pitch,
+                      uint8_t *const *parity_rows /* p pointers */, size_t len, void *stream);
+
+/*
  * Choose the k surviving fragments, in conf-file order (index < k: native, >= k: parity
  * index-k), src/decode.cu:302-307.  Gathers those rows of the total matrix, inverts the k x k
  * matrix with a single-block Gauss-Jordan kernel on the GPU (replaces CPU_invert_matrix,

@@ -499,3 +499,38 @@ def test_batch_of_small_stripes_is_one_call(rs, orc, torch):
     V = orc.gen_encoding_matrix(p, k)
     for s in (0, 7, n - 1):
         assert (got[:, s * L:(s + 1) * L] == orc.matrix_mul(V, stripes[s])).all()
+
+
+# ---- per-row destinations, peer GPUs -----------------------------------------------------
+
+@pytest.mark.parametrize("k,p,L", [(10, 4, 100_000 + 16), (16, 4, 65_536 + 7), (7, 3, 33_333), (32, 8, 40_000), (5, 6, 4096)])
+def test_encode_rows_same_device(rs, orc, torch, k, p, L):
+    data = splitmix64_bytes(8100 + k, k * L).reshape(k, L)
+    want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)
+    d = to_dev(torch, data)
+    rows = [torch.full((L + 64,), 0x77, dtype=torch.uint8, device="cuda") for _ in range(p)]   # separate allocations
+    with rs.RSContext(k, p) as ctx:
+        ctx.encode_rows(d, L, rows, L, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+    for i in range(p):
+        assert (rows[i][:L].cpu().numpy() == want[i]).all()
+        assert bool((rows[i][L:] == 0x77).all())
+
+
+def test_encode_rows_scatter_to_peer_gpu(rs, orc, torch):
+    """Parity rows written straight into another GPU's memory over NVLink (needs >= 2 GPUs)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    k, p, L = 10, 4, 8 * 1024 * 1024 + 48
+    data = splitmix64_bytes(8200, k * L).reshape(k, L)
+    want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)
+    d = to_dev(torch, data)                                                      # on cuda:0
+    rows = [torch.zeros(L, dtype=torch.uint8, device=f"cuda:{i % 2}") for i in range(p)]   # rows 1, 3 on the peer
+    with rs.RSContext(k, p, device=0) as ctx:
+        ctx.enable_peer(1)
+        with torch.cuda.device(0):
+            ctx.encode_rows(d, L, rows, L, torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+    for i in range(p):
+        assert rows[i].device.index == i % 2
+        assert (rows[i].cpu().numpy() == want[i]).all(), f"row {i}"
