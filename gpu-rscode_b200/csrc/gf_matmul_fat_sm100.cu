@@ -44,9 +44,9 @@ __host__ __device__ constexpr int fat8_count(int k)
 __host__ __device__ constexpr int fat_threads(int W, int JB, bool T7)
 {
     // register budget: accumulators (16 or 32, +16 with transposed bit-7 terms) + two batches of JB vectors
-    if (W == 4 && T7) return JB <= 2 ? 768 : (JB <= 4 ? 640 : 512);
-    if (W == 4) return JB <= 2 ? 1024 : (JB <= 4 ? 768 : (JB <= 5 ? 640 : 512));
-    return JB <= 2 ? 768 : (JB <= 5 ? 512 : 384);
+    if (W == 4 && T7) return JB <= 2 ? 768 : (JB <= 4 ? 640 : (JB <= 8 ? 512 : 384));
+    if (W == 4) return JB <= 2 ? 1024 : (JB <= 4 ? 768 : (JB <= 5 ? 640 : (JB <= 8 ? 512 : 384)));
+    return JB <= 2 ? 768 : (JB <= 5 ? 512 : (JB <= 8 ? 384 : 256));
 }
 
 __device__ __forceinline__ uint4 ldg_stream(const uint8_t *p)
@@ -412,6 +412,9 @@ bool pick_fat(int k, FatKernel *fk)
     case 4: *fk = make_fat<W, 4, 1>(); return true;
     case 5: *fk = make_fat<W, 5, 1>(); return true;
     case 6: *fk = make_fat<W, 6, 1>(); return true;
+    case 7: *fk = make_fat<W, 7, 1>(); return true;
+    case 11: *fk = make_fat<W, 11, 1>(); return true;
+    case 13: *fk = make_fat<W, 13, 1>(); return true;
     case 9: *fk = make_fat<W, 3, 3>(); return true;
     case 15: *fk = make_fat<W, 5, 3>(); return true;
     case 18: *fk = make_fat<W, 3, 6>(); return true;
