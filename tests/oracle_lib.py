@@ -173,3 +173,42 @@ class Reference:
 
 def have_reference():
     return os.path.exists(REF_SO) and os.path.exists(REF_BIN)
+
+
+REF_GPU_SO = os.path.join(ORACLE_DIR, "_ref", "libgpurs_ref.so")
+
+
+def have_reference_gpu():
+    return os.path.exists(REF_GPU_SO)
+
+
+class ReferenceGPU:
+    """The reference's own CUDA launchers (src/matrix.cu:752,767,838), recompiled for sm_100a behind
+    oracle/ref_gpu_shim.cu.  Device pointers are plain integers (torch tensors' data_ptr())."""
+
+    MAX_GRID = 2147483647   # what src/encode.cu:351-355 falls back to without -p
+
+    def __init__(self):
+        if not os.path.exists(REF_GPU_SO):
+            raise FileNotFoundError(REF_GPU_SO)
+        L = C.CDLL(REF_GPU_SO)
+        for name in ("refgpu_encode_chunk", "refgpu_decode_chunk"):
+            f = getattr(L, name)
+            f.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
+            f.restype = C.c_float
+        L.refgpu_gen_encoding_matrix.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.refgpu_gen_encoding_matrix.restype = C.c_int
+        self.L = L
+
+    def encode_chunk(self, data_d, coeff_d, code_d, k, p, chunk, grid_x=MAX_GRID):
+        assert k * chunk < 2 ** 31, "the reference indexes with int"
+        return float(self.L.refgpu_encode_chunk(data_d, coeff_d, code_d, k, p, chunk, grid_x))
+
+    def decode_chunk(self, data_d, inv_d, code_d, k, p, chunk, grid_x=MAX_GRID):
+        assert k * chunk < 2 ** 31, "the reference indexes with int"
+        return float(self.L.refgpu_decode_chunk(data_d, inv_d, code_d, k, p, chunk, grid_x))
+
+    def gen_encoding_matrix(self, matrix_d, p, k):
+        rc = self.L.refgpu_gen_encoding_matrix(matrix_d, p, k)
+        if rc:
+            raise RuntimeError(f"reference gen_encoding_matrix: cuda error {rc}")
