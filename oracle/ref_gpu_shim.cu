@@ -5,9 +5,9 @@
 // oracle/_ref/libgpurs_ref.so.  It gives two things ("optional same-box GPU
 // baseline"):
 //   * a second, independent checker on the GPU box: the reference's kernels and ours must write the same
-//     bytes (tests/test_gpu_parity.py::test_reference_gpu_kernels_agree);
-//   * the recompiled reference kernel's own event-timed rate beside ours (tools/ref_gpu_bench.py).
-// Never linked into the product; only tests/ and tools/ load it.
+//     bytes (tests/test_gpu_vs_reference_kernels.py);
+//   * the recompiled reference kernel's own event-timed rate beside ours (tests/tools/ref_gpu_bench.py).
+// Never linked into the product; only tests/ loads it.
 //
 // The reference declares encode_chunk / decode_chunk with C++ linkage (src/matrix.h:80,97), hence this
 // shim.  Their sizes are `int`: k * chunk must stay below 2 GiB.

@@ -5,14 +5,14 @@ engine's kernels on the same device buffers.  The reference times itself with CU
 encode_chunk (matrix.cu:793-823); that number is printed, and an outer CUDA-event bracket around the call
 is printed next to it.  Its sizes are `int`, so k * L stays below 2 GiB (L = 200 MiB for RS(10,14)).
 
-    python tools/ref_gpu_bench.py [--reps 10]
+    python tests/tools/ref_gpu_bench.py [--reps 10]
 """
 import argparse
 import json
 import os
 import sys
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 import torch  # noqa: E402

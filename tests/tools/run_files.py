@@ -2,8 +2,8 @@
 """File-level runs on the GPU box (BASELINE configs C1 and C5-style): the RS binary against the
 reference's own CPU-RS binary on the same file.  Prints one JSON line per case.
 
-    python tools/run_files.py c1                       # RS(4,6), 64 MiB file, erase natives {2,3}
-    python tools/run_files.py big --k 32 --p 8 --gib 2 # host-file encode/decode, all visible GPUs
+    python tests/tools/run_files.py c1                       # RS(4,6), 64 MiB file, erase natives {2,3}
+    python tests/tools/run_files.py big --k 32 --p 8 --gib 2 # host-file encode/decode, all visible GPUs
 """
 import argparse
 import hashlib
@@ -16,7 +16,7 @@ import sys
 import tempfile
 import time
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 from rsdata import splitmix64_bytes  # noqa: E402
 

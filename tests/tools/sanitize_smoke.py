@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Small run of every kernel family for compute-sanitizer (GPU box):
-    compute-sanitizer --tool memcheck python tools/sanitize_smoke.py
+    compute-sanitizer --tool memcheck python tests/tools/sanitize_smoke.py
 Uses raw cudaMalloc'd buffers through the C ABI (no torch), exact-size allocations so that any
 out-of-bounds access of the kernels is visible to the tool, and checks results against the oracle."""
 import importlib
@@ -9,7 +9,7 @@ import sys
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 rs = importlib.import_module("gpu-rscode_b200")
