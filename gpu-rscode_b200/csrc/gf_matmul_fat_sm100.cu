@@ -235,13 +235,20 @@ __device__ __forceinline__ void transpose_store(const uint32_t *a, uint8_t *out,
 // being loaded).  One block per SM leaves too few bytes in flight to cover HBM latency from registers
 // alone; with the prefetch the later register loads hit L2.  Measured: RS(16,20) 0.82 -> 0.92 of the peak.
 // (RS(4,6), already at 0.99 without it, loses 12 % to the extra instructions: PF is per instance.)
-template <int JB, bool PF>
-__device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *&q, size_t in_pitch, uint32_t pf_bytes)
+// PAD: the instance is compiled for K fragments but the code has only k < K (k = 17 runs on the K = 18
+// instance, ...): fragments J0+jj >= k are not loaded -- their tables are all zero, so whatever the
+// registers hold contributes nothing -- and q only moves past them, it is never dereferenced there.
+template <int JB, bool PF, bool PAD, int J0>
+__device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *&q, size_t in_pitch, uint32_t pf_bytes, int k)
 {
 #pragma unroll
     for (int jj = 0; jj < JB; ++jj) {
-        d[jj] = ldg_stream(q);
-        if constexpr (PF) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + pf_bytes));
+        if (!PAD || J0 + jj < k) {
+            d[jj] = ldg_stream(q);
+            if constexpr (PF) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + pf_bytes));
+        } else {
+            d[jj] = make_uint4(0u, 0u, 0u, 0u);
+        }
         q += in_pitch;
     }
 }
@@ -250,33 +257,34 @@ __device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *&q, si
 // buffers alternate per batch ("ping-pong"): the loads of batch t+1 go into the buffer batch t-1 has just
 // released and are issued BEFORE batch t is consumed, so they have a whole batch of work to land and no
 // register-to-register copies are needed.  SP = which buffer holds batch 0 of this column.
-template <int W, int K, int JB, int KB, int B, int SP, bool PF, bool T7>
+template <int W, int K, int JB, int KB, int B, int SP, bool PF, bool T7, bool PAD>
 struct ColumnBatches {
     __device__ __forceinline__ static void run(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
                                                const uint8_t *in, size_t vn, size_t nvec, uint32_t lane_base,
-                                               uint32_t tb, Acc<W> &acc, uint32_t pf0, uint32_t pf1)
+                                               uint32_t tb, Acc<W> &acc, uint32_t pf0, uint32_t pf1, int k)
     {
         constexpr int PAR = (SP + B) & 1;
         uint4 (&cur)[JB] = PAR ? buf1 : buf0;
         uint4 (&nxt)[JB] = PAR ? buf0 : buf1;
         if constexpr (B + 1 < KB) {
-            load_batch<JB, PF>(nxt, q, in_pitch, pf0);
+            load_batch<JB, PF, PAD, (B + 1) * JB>(nxt, q, in_pitch, pf0, k);
         } else {
             if (vn < nvec) {
                 q = in + vn * 16;
-                load_batch<JB, PF>(nxt, q, in_pitch, pf1);
+                load_batch<JB, PF, PAD, 0>(nxt, q, in_pitch, pf1, k);
             }
         }
         BatchMac<W, K, JB, B, 0, T7>::run(cur, lane_base, tb, acc);
         if constexpr (B + 1 < KB)
-            ColumnBatches<W, K, JB, KB, B + 1, SP, PF, T7>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1);
+            ColumnBatches<W, K, JB, KB, B + 1, SP, PF, T7, PAD>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1, k);
     }
 };
 
-template <int W, int K, int JB, int KB, int SP, bool PF, bool T7>
+template <int W, int K, int JB, int KB, int SP, bool PF, bool T7, bool PAD>
 __device__ __forceinline__ void do_column(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
                                           const uint8_t *in, uint8_t *out, size_t out_pitch, size_t v, size_t vn,
-                                          size_t nvec, uint32_t lane_base, uint32_t tb, int nrows, uint32_t pf_stride)
+                                          size_t nvec, uint32_t lane_base, uint32_t tb, int nrows, uint32_t pf_stride,
+                                          int k)
 {
     // L2 prefetch distance in bytes (one grid stride); 0 when that column lies behind the end of the stripe
     const uint32_t pf0 = vn < nvec ? pf_stride : 0u;
@@ -288,7 +296,7 @@ __device__ __forceinline__ void do_column(uint4 (&buf0)[JB], uint4 (&buf1)[JB], 
         if constexpr (W == 8) acc.b[i] = 0;
         else if constexpr (T7) acc.t[i] = 0;
     }
-    ColumnBatches<W, K, JB, KB, 0, SP, PF, T7>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1);
+    ColumnBatches<W, K, JB, KB, 0, SP, PF, T7, PAD>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1, k);
     if constexpr (W == 8) {
         transpose_store(acc.a, out, out_pitch, v * 16, 0, nrows);
         transpose_store(acc.b, out, out_pitch, v * 16, 4, nrows - 4);
@@ -297,10 +305,10 @@ __device__ __forceinline__ void do_column(uint4 (&buf0)[JB], uint4 (&buf1)[JB], 
     }
 }
 
-template <int W, int JB, int KB, bool PF, bool T7>
+template <int W, int JB, int KB, bool PF, bool T7, bool PAD>
 __global__ void __launch_bounds__(fat_threads(W, JB, T7), 1)
 k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
-                const uint32_t *__restrict__ tab, int nrows, size_t nvec)
+                const uint32_t *__restrict__ tab, int nrows, size_t nvec, int k)
 {
     constexpr int K = JB * KB;
     using M = Map<K>;
@@ -332,9 +340,12 @@ k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__rest
             }
             const int x = rem / RV, r = rem - x * RV;
             const uint32_t *tj = tab + (size_t)j * 32 * WW;
-            const uint32_t v0 = __ldg(tj + (x & 15) * WW) ^ __ldg(tj + (16 + (x >> 4)) * WW);
-            uint32_t v1 = v0;
-            if constexpr (W == 8) v1 = __ldg(tj + (x & 15) * WW + 1) ^ __ldg(tj + (16 + (x >> 4)) * WW + 1);
+            uint32_t v0 = 0, v1 = 0;
+            if (!PAD || j < k) {      // padded fragments get all-zero tables (tab holds k fragments)
+                v0 = __ldg(tj + (x & 15) * WW) ^ __ldg(tj + (16 + (x >> 4)) * WW);
+                v1 = v0;
+                if constexpr (W == 8) v1 = __ldg(tj + (x & 15) * WW + 1) ^ __ldg(tj + (16 + (x >> 4)) * WW + 1);
+            }
             const uint32_t base = tb + (j < M::N8 ? j * 32768 : M::N8 * 32768 + (j - M::N8) * 16384);
             asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(base + x * 128 + r * 16), "r"(v0), "r"(v1),
                          "r"(v0), "r"(v1) : "memory");
@@ -342,13 +353,14 @@ k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__rest
     }
     for (int i = tid; i < (K - M::NF) * 32 * WW; i += nt) {   // thin pages: straight copy, 256-byte stride
         const int j = i / (32 * WW), r = i - j * (32 * WW);
-        const uint32_t v = __ldg(tab + (size_t)(M::NF + j) * 32 * WW + r);
+        const uint32_t v = (!PAD || M::NF + j < k) ? __ldg(tab + (size_t)(M::NF + j) * 32 * WW + r) : 0u;
         asm volatile("st.shared.u32 [%0], %1;" ::"r"(tb + M::THIN0 + j * 256 + r * 4), "r"(v) : "memory");
     }
     for (int i = tid; i < K * 4; i += nt) {                   // product of 0x80 = hi-table entry 8
         const int j = i >> 2, q = i & 3;
-        const uint32_t packed = q < WW ? __ldg(tab + (size_t)j * 32 * WW + (16 + 8) * WW + q) : 0u;
-        const uint32_t c = __ldg(tab + (size_t)j * 32 * WW + (16 + 8) * WW);
+        const bool real = !PAD || j < k;
+        const uint32_t packed = (real && q < WW) ? __ldg(tab + (size_t)j * 32 * WW + (16 + 8) * WW + q) : 0u;
+        const uint32_t c = real ? __ldg(tab + (size_t)j * 32 * WW + (16 + 8) * WW) : 0u;
         const uint32_t repl = ((c >> (8 * q)) & 0xFFu) * 0x01010101u;   // rows 0..3, one per word
         asm volatile("st.shared.u32 [%0], %1;" ::"r"(tb + M::C7 + i * 4), "r"(packed) : "memory");
         asm volatile("st.shared.u32 [%0], %1;" ::"r"(tb + M::C7R + i * 4), "r"(repl) : "memory");
@@ -362,20 +374,20 @@ k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__rest
     const uint32_t pf_stride = (uint32_t)(stride * 16);
     uint4 buf0[JB], buf1[JB];
     const uint8_t *q = in + v * 16;
-    if (v < nvec) load_batch<JB, PF>(buf0, q, in_pitch, v + stride < nvec ? pf_stride : 0u);
+    if (v < nvec) load_batch<JB, PF, PAD, 0>(buf0, q, in_pitch, v + stride < nvec ? pf_stride : 0u, k);
 
     while (v < nvec) {
-        do_column<W, K, JB, KB, 0, PF, T7>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride);
+        do_column<W, K, JB, KB, 0, PF, T7, PAD>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride, k);
         v += stride;
         if constexpr (KB & 1) {          // odd batch count: the next column starts in the other buffer
             if (v >= nvec) break;
-            do_column<W, K, JB, KB, 1, PF, T7>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride);
+            do_column<W, K, JB, KB, 1, PF, T7, PAD>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride, k);
             v += stride;
         }
     }
 }
 
-using FatFn = void (*)(const uint8_t *, size_t, uint8_t *, size_t, const uint32_t *, int, size_t);
+using FatFn = void (*)(const uint8_t *, size_t, uint8_t *, size_t, const uint32_t *, int, size_t, int);
 
 struct FatKernel {
     FatFn fn;
@@ -383,7 +395,7 @@ struct FatKernel {
     int smem;
 };
 
-template <int W, int JB, int KB>
+template <int W, int JB, int KB, bool PAD = false>
 FatKernel make_fat()
 {
     // L2 prefetch one stride ahead: on from k = 8.  Same box, same build, off -> on (fraction of the measured
@@ -396,7 +408,7 @@ FatKernel make_fat()
     // (RS(10,14) 0.930 -> 0.754, RS(12,16) 0.878 -> 0.639).
     constexpr int K = JB * KB;
     constexpr bool T7 = (W == 4) && (K == 12 || K == 14 || K == 16 || K == 18 || K == 20);
-    return FatKernel{k_gf_matmul_fat<W, JB, KB, PF, T7>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
+    return FatKernel{k_gf_matmul_fat<W, JB, KB, PF, T7, PAD>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
 }
 
 // Batch shape per k (JB fragments per batch x KB batches), measured on B200: batches of 4 with 768
@@ -408,6 +420,7 @@ template <int W>
 bool pick_fat(int k, FatKernel *fk)
 {
     switch (k) {
+    case 2: *fk = make_fat<W, 2, 1>(); return true;
     case 3: *fk = make_fat<W, 3, 1>(); return true;
     case 4: *fk = make_fat<W, 4, 1>(); return true;
     case 5: *fk = make_fat<W, 5, 1>(); return true;
@@ -426,8 +439,15 @@ bool pick_fat(int k, FatKernel *fk)
     case 20: *fk = make_fat<W, 5, 4>(); return true;
     case 24: *fk = make_fat<W, 4, 6>(); return true;
     case 32: *fk = make_fat<W, 4, 8>(); return true;
-    default: return false;
+    default: break;
     }
+    // k without an instance of its own runs on the next larger one with all-zero tables for the missing
+    // fragments (their loads are skipped): a few wasted lookups, still one lookup per real input byte
+    if (k == 17) { *fk = make_fat<W, 3, 6, true>(); return true; }
+    if (k == 19) { *fk = make_fat<W, 5, 4, true>(); return true; }
+    if (k >= 21 && k <= 23) { *fk = make_fat<W, 4, 6, true>(); return true; }
+    if (k >= 30 && k <= 31) { *fk = make_fat<W, 4, 8, true>(); return true; }   // k = 28: 0.633 vs 0.674 split-nibble
+    return false;
 }
 
 }  // namespace
@@ -449,7 +469,7 @@ cudaError_t launch_matmul_fat(const RowGroup &g, int k, const uint8_t *in, size_
     size_t cap = (size_t)dev.sm_count;      // one block per SM: the tables fill its shared memory
     if (max_blocks > 0 && (size_t)max_blocks < cap) cap = max_blocks;
     const unsigned grid = (unsigned)(want < cap ? want : cap);
-    fk.fn<<<grid, fk.threads, fk.smem, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, g.nrows, nvec);
+    fk.fn<<<grid, fk.threads, fk.smem, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, g.nrows, nvec, k);
     return cudaGetLastError();
 }
 

@@ -132,7 +132,7 @@ def test_encode_variants_vs_oracle(rs, orc, torch, variant, k, p, L):
     assert (got == orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)).all()
 
 
-@pytest.mark.parametrize("k", [3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 24, 32])
+@pytest.mark.parametrize("k", [2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22, 23, 24, 27, 29, 31, 32])
 @pytest.mark.parametrize("p", [1, 4, 5, 8])
 def test_encode_bank_replicated_kernel_vs_oracle(rs, orc, torch, k, p):
     """variant 5 forces the byte-table kernel (fat8 / fat7 / nibble mix depends on k) at a small size."""
