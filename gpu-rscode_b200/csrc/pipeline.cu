@@ -114,7 +114,7 @@ int rsgpu_decode_host(rsgpu_ctx *c, const uint8_t *surv, size_t surv_pitch, uint
     if (c->k > 1 && (surv_pitch < len || natives_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
     int rc = ctx_bind(c);
     if (rc) return rc;
-    return pipeline_run(c, c->dec_full, surv, surv_pitch, natives, natives_pitch, len, slots);
+    return pipeline_run(c, c->dec_full(), surv, surv_pitch, natives, natives_pitch, len, slots);
 }
 
 int rsgpu_decode_erased_host(rsgpu_ctx *c, const uint8_t *surv, size_t surv_pitch, uint8_t *out, size_t out_pitch,
@@ -127,7 +127,7 @@ int rsgpu_decode_erased_host(rsgpu_ctx *c, const uint8_t *surv, size_t surv_pitc
     if ((c->k > 1 && surv_pitch < len) || (c->n_erased > 1 && out_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
     int rc = ctx_bind(c);
     if (rc) return rc;
-    return pipeline_run(c, c->dec_erased, surv, surv_pitch, out, out_pitch, len, slots);
+    return pipeline_run(c, c->dec_erased(), surv, surv_pitch, out, out_pitch, len, slots);
 }
 
 }  // extern "C"

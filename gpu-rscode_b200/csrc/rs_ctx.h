@@ -19,11 +19,22 @@ struct rsgpu_ctx {
     int *d_flag = nullptr;        // singular flag written by the inversion kernel
 
     rsgpu::Plan enc;              // p x k generator
-    rsgpu::Plan dec_full;         // k x k inverse (reference-semantic decode)
-    rsgpu::Plan dec_erased;       // e x k rows of the inverse for the erased natives
+    // Decode plans come in two sets used alternately: rsgpu_set_survivors builds into the set that is NOT
+    // current, ordered (cudaStreamWaitEvent) after the last kernel that read that set, and only then makes
+    // it current -- a decode still in flight on the caller's stream keeps reading intact tables.
+    struct DecodeSet {
+        rsgpu::Plan full;         // k x k inverse (reference-semantic decode)
+        rsgpu::Plan erased;       // e x k rows of the inverse for the erased natives
+        cudaEvent_t last_use = nullptr;
+    };
+    DecodeSet dec[2];
+    int dec_cur = 0;
+    rsgpu::Plan &dec_full() { return dec[dec_cur].full; }
+    rsgpu::Plan &dec_erased() { return dec[dec_cur].erased; }
     rsgpu::Plan scratch;          // rsgpu_matmul's caller-supplied matrix
     rsgpu::Plan repair;           // m x k: T[wanted] * inverse, rebuilds any wanted fragments
     bool have_repair = false;
+    cudaEvent_t repair_last_use = nullptr;   // same ordering for rsgpu_set_repair after rsgpu_repair
 
     bool have_survivors = false;
     int survivors[256];

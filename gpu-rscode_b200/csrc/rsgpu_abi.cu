@@ -139,6 +139,9 @@ static int ctx_create(rsgpu_ctx **out, int device, int k, int p, const uint8_t *
     if ((e = cudaMalloc(&c->d_rows, sizeof(int) * 256)) != cudaSuccess) return bail(fail_cuda(e, "cudaMalloc row list"));
     if ((e = cudaMalloc(&c->d_flag, sizeof(int))) != cudaSuccess) return bail(fail_cuda(e, "cudaMalloc flag"));
 
+    for (cudaEvent_t *ev : {&c->dec[0].last_use, &c->dec[1].last_use, &c->repair_last_use})
+        if ((e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming)) != cudaSuccess) return bail(fail_cuda(e, "cudaEventCreate"));
+
     cudaStream_t s = c->setup_stream;
     if ((e = launch_build_gf_tables(c->gf.d_exp, c->gf.d_log, s)) != cudaSuccess) return bail(fail_cuda(e, "build_gf_tables"));
     ++c->launches;
@@ -219,8 +222,12 @@ void rsgpu_destroy(rsgpu_ctx *c)
     cudaSetDevice(c->device);
     pipeline_free(c);
     plan_free(c->enc);
-    plan_free(c->dec_full);
-    plan_free(c->dec_erased);
+    for (auto &ds : c->dec) {
+        plan_free(ds.full);
+        plan_free(ds.erased);
+        if (ds.last_use) cudaEventDestroy(ds.last_use);
+    }
+    if (c->repair_last_use) cudaEventDestroy(c->repair_last_use);
     plan_free(c->scratch);
     plan_free(c->repair);
     if (c->gf.d_exp) cudaFree(c->gf.d_exp);
@@ -303,36 +310,49 @@ int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
     }
     int rc = ctx_bind(c);
     if (rc) return rc;
-    c->dec_full.valid = false;
-    c->dec_erased.valid = false;
+    // Build into the set that is not current; a failure below leaves the context without survivors.
+    c->have_survivors = false;
+    rsgpu_ctx::DecodeSet &ds = c->dec[c->dec_cur ^ 1];
+    ds.full.valid = false;
+    ds.erased.valid = false;
     c->n_erased = 0;
     for (int j = 0; j < k; ++j)
         if (!have[j]) c->erased[c->n_erased++] = j;
     memcpy(c->survivors, idx, sizeof(int) * k);
 
     cudaStream_t s = c->setup_stream;
-    if (!c->dec_full.d_matrix && (rc = plan_alloc(c->dec_full, k, k)) != RSGPU_OK) return rc;
+    CK(cudaStreamWaitEvent(s, ds.last_use, 0));   // the last decode that read this set's tables has finished
+    if (!ds.full.d_matrix && (rc = plan_alloc(ds.full, k, k)) != RSGPU_OK) return rc;
     CK(cudaMemcpyAsync(c->d_rows, idx, sizeof(int) * k, cudaMemcpyHostToDevice, s));
     CK(launch_gather_rows(c->d_total, k, c->d_rows, k, c->d_sub, s));
-    CK(launch_gj_invert(c->d_sub, c->dec_full.d_matrix, k, c->d_flag, c->gf, s));
+    CK(launch_gj_invert(c->d_sub, ds.full.d_matrix, k, c->d_flag, c->gf, s));
     c->launches += 2;
     int flag = 0;
     CK(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     if (flag) return fail_msg(RSGPU_ESINGULAR, "the chosen survivors give a singular matrix");
-    if ((rc = plan_build_tables(c, c->dec_full, s)) != RSGPU_OK) return rc;
+    if ((rc = plan_build_tables(c, ds.full, s)) != RSGPU_OK) return rc;
 
     if (c->n_erased > 0) {
-        if (c->dec_erased.rows != c->n_erased || !c->dec_erased.d_matrix)
-            if ((rc = plan_alloc(c->dec_erased, c->n_erased, k)) != RSGPU_OK) return rc;
+        if (ds.erased.rows != c->n_erased || !ds.erased.d_matrix)
+            if ((rc = plan_alloc(ds.erased, c->n_erased, k)) != RSGPU_OK) return rc;
         // rows of the inverse that rebuild the erased natives
         CK(cudaMemcpyAsync(c->d_rows, c->erased, sizeof(int) * c->n_erased, cudaMemcpyHostToDevice, s));
-        CK(launch_gather_rows(c->dec_full.d_matrix, k, c->d_rows, c->n_erased, c->dec_erased.d_matrix, s));
+        CK(launch_gather_rows(ds.full.d_matrix, k, c->d_rows, c->n_erased, ds.erased.d_matrix, s));
         ++c->launches;
-        if ((rc = plan_build_tables(c, c->dec_erased, s)) != RSGPU_OK) return rc;
+        if ((rc = plan_build_tables(c, ds.erased, s)) != RSGPU_OK) return rc;
     }
     CK(cudaStreamSynchronize(s));
+    c->dec_cur ^= 1;
     c->have_survivors = true;
+    return RSGPU_OK;
+}
+
+// After a kernel that reads the current decode set has been queued on `s`: remember it for the ordering
+// in rsgpu_set_survivors.
+static int mark_decode_use(rsgpu_ctx *c, cudaStream_t s)
+{
+    CK(cudaEventRecord(c->dec[c->dec_cur].last_use, s));
     return RSGPU_OK;
 }
 
@@ -347,12 +367,13 @@ int rsgpu_set_repair(rsgpu_ctx *c, const int *survivors, const int *wanted, int 
     if (rc != RSGPU_OK) return rc;
     const int k = c->k;
     cudaStream_t s = c->setup_stream;
+    CK(cudaStreamWaitEvent(s, c->repair_last_use, 0));   // the last rsgpu_repair has finished with the old tables
     if (c->repair.rows != n_wanted || !c->repair.d_matrix)
         if ((rc = plan_alloc(c->repair, n_wanted, k)) != RSGPU_OK) return rc;
     // repair matrix = (rows `wanted` of the total matrix) x inverse: natives come out as rows of the
     // inverse, parities as generator rows applied to the reconstructed natives, in one multiply
     CK(cudaMemcpyAsync(c->d_rows, wanted, sizeof(int) * n_wanted, cudaMemcpyHostToDevice, s));
-    CK(launch_rows_times_matrix(c->d_total, c->d_rows, n_wanted, c->dec_full.d_matrix, k, c->repair.d_matrix, c->gf, s));
+    CK(launch_rows_times_matrix(c->d_total, c->d_rows, n_wanted, c->dec_full().d_matrix, k, c->repair.d_matrix, c->gf, s));
     ++c->launches;
     if ((rc = plan_build_tables(c, c->repair, s)) != RSGPU_OK) return rc;
     CK(cudaStreamSynchronize(s));
@@ -368,7 +389,9 @@ int rsgpu_repair(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, uint8_t
     if ((c->k > 1 && surv_pitch < len) || (c->repair.rows > 1 && out_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
     int rc = ctx_bind(c);
     if (rc) return rc;
-    return plan_apply(c, c->repair, surv_d, surv_pitch, out_d, out_pitch, len, (cudaStream_t)stream);
+    if ((rc = plan_apply(c, c->repair, surv_d, surv_pitch, out_d, out_pitch, len, (cudaStream_t)stream)) != RSGPU_OK) return rc;
+    CK(cudaEventRecord(c->repair_last_use, (cudaStream_t)stream));
+    return RSGPU_OK;
 }
 
 int rsgpu_get_decode_matrix(rsgpu_ctx *c, uint8_t *inverse)
@@ -377,7 +400,7 @@ int rsgpu_get_decode_matrix(rsgpu_ctx *c, uint8_t *inverse)
     if (!c->have_survivors) return fail_msg(RSGPU_ESTATE, "rsgpu_set_survivors has not succeeded yet");
     int rc = ctx_bind(c);
     if (rc) return rc;
-    CK(cudaMemcpy(inverse, c->dec_full.d_matrix, (size_t)c->k * c->k, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(inverse, c->dec_full().d_matrix, (size_t)c->k * c->k, cudaMemcpyDeviceToHost));
     return RSGPU_OK;
 }
 
@@ -398,7 +421,8 @@ int rsgpu_decode(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, uint8_t
     if (c->k > 1 && (surv_pitch < len || nat_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
     int rc = ctx_bind(c);
     if (rc) return rc;
-    return plan_apply(c, c->dec_full, surv_d, surv_pitch, nat_d, nat_pitch, len, (cudaStream_t)stream);
+    if ((rc = plan_apply(c, c->dec_full(), surv_d, surv_pitch, nat_d, nat_pitch, len, (cudaStream_t)stream)) != RSGPU_OK) return rc;
+    return mark_decode_use(c, (cudaStream_t)stream);
 }
 
 int rsgpu_decode_erased(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, uint8_t *out_d, size_t out_pitch,
@@ -411,7 +435,8 @@ int rsgpu_decode_erased(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, 
     if ((c->k > 1 && surv_pitch < len) || (c->n_erased > 1 && out_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
     int rc = ctx_bind(c);
     if (rc) return rc;
-    return plan_apply(c, c->dec_erased, surv_d, surv_pitch, out_d, out_pitch, len, (cudaStream_t)stream);
+    if ((rc = plan_apply(c, c->dec_erased(), surv_d, surv_pitch, out_d, out_pitch, len, (cudaStream_t)stream)) != RSGPU_OK) return rc;
+    return mark_decode_use(c, (cudaStream_t)stream);
 }
 
 int rsgpu_invert_matrix(rsgpu_ctx *c, const uint8_t *matrix, uint8_t *inverse, int n)

@@ -119,6 +119,10 @@ int rsgpu_encode_rows(rsgpu_ctx *ctx, const uint8_t *data_d, size_t data_pitch,
  * Returns RSGPU_ESINGULAR when the survivors cannot reconstruct the data (the reference cannot
  * detect this).  Row pivoting is used, so the result is the true inverse for every invertible
  * input, and equals the reference's wherever the reference is correct.
+ * May be called while an rsgpu_decode / rsgpu_decode_erased of the previous survivor set is still
+ * running on the caller's stream: the new tables go to a second buffer (two sets, used alternately,
+ * re-use ordered by an event), so that decode finishes with the tables it started with.  After a
+ * failure the context has no survivors (decode returns RSGPU_ESTATE) until a call succeeds.
  */
 int rsgpu_set_survivors(rsgpu_ctx *ctx, const int *fragment_index /* k entries */);
 

@@ -315,6 +315,39 @@ def test_decode_roundtrip_and_oracle(rs, orc, torch, k, p, order, L):
             assert (out_e.cpu().numpy() == data[erased]).all()
 
 
+def test_set_survivors_while_previous_decode_is_in_flight(rs, torch):
+    """rsgpu_set_survivors for the NEXT survivor set may be called while decodes of the previous set are
+    still queued: each decode must finish with the tables it was launched with (two plan sets, event
+    ordered).  Long stripes keep the kernels busy while the host races ahead."""
+    k, p, L = 10, 4, 48 << 20
+    stream = torch.cuda.current_stream().cuda_stream
+    data = torch.randint(0, 256, (k, L), dtype=torch.uint8, device="cuda")
+    orders = [[10, 11, 12, 13, 4, 5, 6, 7, 8, 9], [0, 1, 2, 3, 4, 5, 10, 11, 12, 13], [13, 1, 12, 3, 11, 5, 10, 7, 8, 9],
+              list(range(10)), [0, 11, 2, 13, 4, 5, 6, 7, 12, 9]]
+    with rs.RSContext(k, p) as ctx:
+        parity = torch.empty((p, L), dtype=torch.uint8, device="cuda")
+        ctx.encode(data.data_ptr(), L, parity.data_ptr(), L, L, stream)
+        frags = torch.cat([data, parity])
+        survs = [frags[torch.tensor(o, device="cuda")].contiguous() for o in orders]
+        outs = [torch.empty((k, L), dtype=torch.uint8, device="cuda") for _ in range(3 * len(orders))]
+        torch.cuda.synchronize()
+        for i, out in enumerate(outs):            # no synchronisation between the steps
+            o = i % len(orders)
+            ctx.set_survivors(orders[o])
+            if i % 2:
+                ctx.decode(survs[o].data_ptr(), L, out.data_ptr(), L, L, stream)
+            else:
+                out.copy_(data)                   # decode_erased writes only the lost natives
+                er = ctx.erased()
+                if er:
+                    tmp = torch.empty((len(er), L), dtype=torch.uint8, device="cuda")
+                    ctx.decode_erased(survs[o].data_ptr(), L, tmp.data_ptr(), L, L, stream)
+                    out[torch.tensor(er, device="cuda")] = tmp
+        torch.cuda.synchronize()
+        for i, out in enumerate(outs):
+            assert torch.equal(out, data), f"step {i}"
+
+
 def test_gpu_encode_then_gpu_decode_all_double_erasures_rs46(rs, torch):
     k, p, L = 4, 2, 3_001
     data = splitmix64_bytes(9, k * L).reshape(k, L)
