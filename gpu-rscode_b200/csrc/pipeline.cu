@@ -42,11 +42,17 @@ static int pipeline_ensure(rsgpu_ctx *c, int slots, size_t pitch, int in_rows, i
         pipeline_free(c);
     }
     for (int i = 0; i < slots; ++i) {
-        CK(cudaStreamCreateWithFlags(&c->slot_stream[i], cudaStreamNonBlocking));
-        cudaError_t e = cudaMalloc(&c->slot_in[i], pitch * in_rows);
+        cudaError_t e = cudaStreamCreateWithFlags(&c->slot_stream[i], cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaMalloc(&c->slot_in[i], pitch * in_rows);
         if (e == cudaSuccess) e = cudaMalloc(&c->slot_out[i], pitch * out_rows);
-        if (e == cudaErrorMemoryAllocation) return fail_msg(RSGPU_ENOMEM, "device allocation for pipeline slots failed");
-        if (e != cudaSuccess) return fail_cuda(e, "cudaMalloc pipeline slot");
+        if (e != cudaSuccess) {
+            pipeline_free(c);   // a half-built ring is of no use; the next call starts over
+            if (e == cudaErrorMemoryAllocation) {
+                cudaGetLastError();
+                return fail_msg(RSGPU_ENOMEM, "device allocation for pipeline slots failed");
+            }
+            return fail_cuda(e, "pipeline slot set-up");
+        }
     }
     c->n_slots = slots;
     c->slot_pitch = pitch;
@@ -78,15 +84,24 @@ static int pipeline_run(rsgpu_ctx *c, const Plan &pl, const uint8_t *in, size_t 
     if (rc) return rc;
     const size_t pitch = c->slot_pitch;
     int slot = 0;
-    for (size_t off = 0; off < len; off += slice, slot = (slot + 1) % slots) {
+    for (size_t off = 0; off < len && rc == RSGPU_OK; off += slice, slot = (slot + 1) % slots) {
         const size_t cur = len - off < slice ? len - off : slice;
         cudaStream_t s = c->slot_stream[slot];
-        CK(cudaMemcpy2DAsync(c->slot_in[slot], pitch, in + off, in_pitch, cur, pl.k, cudaMemcpyHostToDevice, s));
-        if ((rc = plan_apply(c, pl, c->slot_in[slot], pitch, c->slot_out[slot], pitch, cur, s)) != RSGPU_OK) return rc;
-        CK(cudaMemcpy2DAsync(out + off, out_pitch, c->slot_out[slot], pitch, cur, pl.rows, cudaMemcpyDeviceToHost, s));
+        cudaError_t e = cudaMemcpy2DAsync(c->slot_in[slot], pitch, in + off, in_pitch, cur, pl.k, cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) {
+            rc = fail_cuda(e, "host-to-device slice copy");
+            break;
+        }
+        if ((rc = plan_apply(c, pl, c->slot_in[slot], pitch, c->slot_out[slot], pitch, cur, s)) != RSGPU_OK) break;
+        e = cudaMemcpy2DAsync(out + off, out_pitch, c->slot_out[slot], pitch, cur, pl.rows, cudaMemcpyDeviceToHost, s);
+        if (e != cudaSuccess) rc = fail_cuda(e, "device-to-host slice copy");
     }
-    for (int i = 0; i < slots; ++i) CK(cudaStreamSynchronize(c->slot_stream[i]));
-    return RSGPU_OK;
+    // drain every slot even after a failure: the caller's buffers must not be touched after we return
+    for (int i = 0; i < slots; ++i) {
+        cudaError_t e = cudaStreamSynchronize(c->slot_stream[i]);
+        if (e != cudaSuccess && rc == RSGPU_OK) rc = fail_cuda(e, "pipeline drain");
+    }
+    return rc;
 }
 
 }  // namespace rsgpu

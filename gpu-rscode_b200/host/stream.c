@@ -289,6 +289,12 @@ int rs_stream_run(const rs_stream_desc *desc, double *wall_ms, int *n_gpus_used,
     st.slot = calloc((size_t)st.n_slots, sizeof(slot_t));
     st.q_cap = st.n_slots * (desc->in_rows + desc->n_dst + 2) + 8;
     st.queue = calloc((size_t)st.q_cap, sizeof(task_t));
+    if (!st.slot || !st.queue) {
+        free(st.slot);
+        free(st.queue);
+        snprintf(error_text, error_cap, "out of host memory");
+        return RSGPU_ENOMEM;
+    }
     for (int i = 0; i < st.n_slots; ++i) {
         st.slot[i].slab = -1;
         st.slot[i].state = ST_FREE;
@@ -297,6 +303,12 @@ int rs_stream_run(const rs_stream_desc *desc, double *wall_ms, int *n_gpus_used,
             rc = rsgpu_host_alloc((void **)&st.slot[i].out, (size_t)(desc->out_rows > 0 ? desc->out_rows : 1) * st.slab_bytes);
         if (rc != RSGPU_OK) {
             snprintf(error_text, error_cap, "pinned allocation failed: %s (%s)", rsgpu_strerror(rc), rsgpu_last_error());
+            for (int j = 0; j <= i; ++j) {
+                rsgpu_host_free(st.slot[j].in);
+                rsgpu_host_free(st.slot[j].out);
+            }
+            free(st.slot);
+            free(st.queue);
             return rc;
         }
     }
@@ -313,11 +325,24 @@ int rs_stream_run(const rs_stream_desc *desc, double *wall_ms, int *n_gpus_used,
     gpu_arg_t *ga = calloc((size_t)st.n_gpus, sizeof(gpu_arg_t));
     const double t0 = now_s();
     st.t_start = t0;
-    for (int i = 0; i < st.n_io; ++i) pthread_create(&io[i], NULL, io_main, &st);
-    for (int g = 0; g < st.n_gpus; ++g) {
-        ga[g].st = &st;
-        ga[g].gpu = g;
-        pthread_create(&gp[g], NULL, gpu_main, &ga[g]);
+    /* a thread that cannot be started is simply not there: fewer IO threads are slower, not wrong; with no
+     * IO thread or no GPU worker at all the job is stopped with an error */
+    int io_started = 0, gpu_started = 0;
+    if (io && gp && ga) {
+        for (int i = 0; i < st.n_io; ++i)
+            if (pthread_create(&io[io_started], NULL, io_main, &st) == 0) ++io_started;
+        for (int g = 0; g < st.n_gpus; ++g) {
+            ga[gpu_started].st = &st;
+            ga[gpu_started].gpu = g;
+            if (pthread_create(&gp[gpu_started], NULL, gpu_main, &ga[gpu_started]) == 0) ++gpu_started;
+        }
+    }
+    st.n_io = io_started;
+    st.n_gpus = gpu_started;
+    if (io_started == 0 || gpu_started == 0) {
+        pthread_mutex_lock(&st.mu);
+        set_error(&st, RSGPU_ENOMEM, "could not start the IO / GPU worker threads");
+        pthread_mutex_unlock(&st.mu);
     }
 
     /* feeder: hand slabs to free slots in order */
