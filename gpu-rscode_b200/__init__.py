@@ -37,6 +37,7 @@ ABI_SYMBOLS = [
     "rsgpu_host_free", "rsgpu_host_register", "rsgpu_host_unregister", "rsgpu_dev_alloc", "rsgpu_dev_free",
     "rsgpu_memcpy_h2d", "rsgpu_memcpy_d2h", "rsgpu_sync", "rsgpu_set_tuning", "rsgpu_launch_count",
     "rsgpu_encode_noalloc", "rsgpu_create_generator", "rsgpu_set_repair", "rsgpu_repair", "rsgpu_enable_peer", "rsgpu_encode_rows",
+    "rsgpu_encode_batch", "rsgpu_decode_erased_batch",
 ]
 
 
@@ -80,6 +81,8 @@ def lib():
     L.rsgpu_repair.argtypes = [vp, u8p, sz, u8p, sz, sz, vp]
     L.rsgpu_enable_peer.argtypes = [vp, i32]
     L.rsgpu_encode_rows.argtypes = [vp, u8p, sz, C.POINTER(vp), sz, vp]
+    L.rsgpu_encode_batch.argtypes = [vp, u8p, sz, sz, u8p, sz, sz, sz, sz, vp]
+    L.rsgpu_decode_erased_batch.argtypes = [vp, u8p, sz, sz, u8p, sz, sz, sz, sz, vp]
     L.rsgpu_destroy.argtypes = [vp]
     L.rsgpu_destroy.restype = None
     for f in ("rsgpu_k", "rsgpu_p", "rsgpu_device"):
@@ -222,6 +225,17 @@ class RSContext:
     # -- device-pointer coding ----------------------------------------------------------------
     def encode(self, data_d, data_pitch, parity_d, parity_pitch, length, stream=0):
         _check(lib().rsgpu_encode(self._h, _ptr(data_d), data_pitch, _ptr(parity_d), parity_pitch, length, stream))
+
+    def encode_batch(self, data_d, data_pitch, data_stripe_pitch, parity_d, parity_pitch, parity_stripe_pitch, length,
+                     n_stripes, stream=0):
+        """n_stripes stripes in one call: fragment j of stripe s at data_d + s*data_stripe_pitch + j*data_pitch."""
+        _check(lib().rsgpu_encode_batch(self._h, _ptr(data_d), data_pitch, data_stripe_pitch, _ptr(parity_d), parity_pitch,
+                                        parity_stripe_pitch, length, n_stripes, stream))
+
+    def decode_erased_batch(self, surv_d, surv_pitch, surv_stripe_pitch, out_d, out_pitch, out_stripe_pitch, length,
+                            n_stripes, stream=0):
+        _check(lib().rsgpu_decode_erased_batch(self._h, _ptr(surv_d), surv_pitch, surv_stripe_pitch, _ptr(out_d), out_pitch,
+                                               out_stripe_pitch, length, n_stripes, stream))
 
     def enable_peer(self, peer_device):
         _check(lib().rsgpu_enable_peer(self._h, peer_device))

@@ -101,6 +101,13 @@ cudaError_t launch_matmul_fat(const RowGroup &g, int k, const uint8_t *in, size_
                               cudaStream_t s);
 
 
+// ---- gf_matmul_fat_batch_sm100.cu ---------------------------------------------------------------
+// A batch of n_stripes stripes in ONE launch: fragment j of stripe s at in + s*in_stripe + j*in_pitch.
+// cudaErrorNotSupported when there is no instance for k (the caller then launches per stripe).
+cudaError_t launch_matmul_fat_batch(const RowGroup &g, int k, const uint8_t *in, size_t in_pitch, size_t in_stripe,
+                                    uint8_t *out_g, size_t out_pitch, size_t out_stripe, size_t nvec, size_t n_stripes,
+                                    const DeviceInfo &dev, int max_blocks, cudaStream_t s);
+
 // ---- gf_matmul_rows_sm100.cu --------------------------------------------------------------------
 // One destination pointer per output row (rows may be peer-GPU memory: the stores go over NVLink).
 cudaError_t launch_matmul_rows(const RowGroup &g, int k, int kpad, const uint8_t *in, size_t in_pitch,

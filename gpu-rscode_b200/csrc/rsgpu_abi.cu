@@ -96,6 +96,40 @@ int plan_apply(rsgpu_ctx *c, const Plan &pl, const uint8_t *in, size_t in_pitch,
     return RSGPU_OK;
 }
 
+// A batch of stripes through one plan.  One launch per row group when the batch kernel applies (16-byte
+// aligned geometry, an instance for k, enough bytes to pay for the table build); otherwise stripe by stripe.
+int plan_apply_batch(rsgpu_ctx *c, const Plan &pl, const uint8_t *in, size_t in_pitch, size_t in_stripe, uint8_t *out,
+                     size_t out_pitch, size_t out_stripe, size_t len, size_t n_stripes, cudaStream_t s)
+{
+    if (!pl.valid) return fail_msg(RSGPU_ESTATE, "coding plan not built");
+    if (len == 0 || n_stripes == 0) return RSGPU_OK;
+    const bool aligned = (((uintptr_t)in | (uintptr_t)out | in_pitch | out_pitch | in_stripe | out_stripe | len) & 15u) == 0;
+    const bool want = n_stripes > 1 && aligned && (c->tune.variant == 0 || c->tune.variant == 5) &&
+                      (c->tune.variant == 5 || len * n_stripes >= ((size_t)2 << 20));
+    if (want) {
+        bool done = true;
+        for (int g = 0; g < pl.ngroups && done; ++g) {
+            const RowGroup &rg = pl.grp[g];
+            cudaError_t e = launch_matmul_fat_batch(rg, pl.k, in, in_pitch, in_stripe, out + (size_t)rg.row0 * out_pitch, out_pitch,
+                                                    out_stripe, len / 16, n_stripes, c->dev, c->tune.max_blocks, s);
+            if (e == cudaErrorNotSupported) {
+                if (g != 0) return fail_msg(RSGPU_ECUDA, "batch kernel support differs between row groups");
+                done = false;   // no instance for this k: fall through to the per-stripe launches
+            } else if (e != cudaSuccess) {
+                return fail_cuda(e, "launch_matmul_fat_batch");
+            } else {
+                ++c->launches;
+            }
+        }
+        if (done) return RSGPU_OK;
+    }
+    for (size_t st = 0; st < n_stripes; ++st) {
+        int rc = plan_apply(c, pl, in + st * in_stripe, in_pitch, out + st * out_stripe, out_pitch, len, s);
+        if (rc != RSGPU_OK) return rc;
+    }
+    return RSGPU_OK;
+}
+
 int ctx_bind(const rsgpu_ctx *c)
 {
     CK(cudaSetDevice(c->device));
@@ -262,6 +296,19 @@ int rsgpu_encode(rsgpu_ctx *c, const uint8_t *data_d, size_t data_pitch, uint8_t
     int rc = ctx_bind(c);
     if (rc) return rc;
     return plan_apply(c, c->enc, data_d, data_pitch, parity_d, parity_pitch, len, (cudaStream_t)stream);
+}
+
+int rsgpu_encode_batch(rsgpu_ctx *c, const uint8_t *data_d, size_t data_pitch, size_t data_stripe_pitch, uint8_t *parity_d,
+                       size_t parity_pitch, size_t parity_stripe_pitch, size_t len, size_t n_stripes, void *stream)
+{
+    if (!c || !data_d || !parity_d) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (c->p == 0) return RSGPU_OK;
+    if ((c->k > 1 && data_pitch < len) || (c->p > 1 && parity_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
+    if (n_stripes > 1 && (data_stripe_pitch < len || parity_stripe_pitch < len)) return fail_msg(RSGPU_EINVAL, "stripe pitch < len");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    return plan_apply_batch(c, c->enc, data_d, data_pitch, data_stripe_pitch, parity_d, parity_pitch, parity_stripe_pitch, len,
+                            n_stripes, (cudaStream_t)stream);
 }
 
 int rsgpu_enable_peer(rsgpu_ctx *c, int peer_device)
@@ -436,6 +483,23 @@ int rsgpu_decode_erased(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, 
     int rc = ctx_bind(c);
     if (rc) return rc;
     if ((rc = plan_apply(c, c->dec_erased(), surv_d, surv_pitch, out_d, out_pitch, len, (cudaStream_t)stream)) != RSGPU_OK) return rc;
+    return mark_decode_use(c, (cudaStream_t)stream);
+}
+
+int rsgpu_decode_erased_batch(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, size_t surv_stripe_pitch, uint8_t *out_d,
+                              size_t out_pitch, size_t out_stripe_pitch, size_t len, size_t n_stripes, void *stream)
+{
+    if (!c || !surv_d) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if (!c->have_survivors) return fail_msg(RSGPU_ESTATE, "rsgpu_set_survivors has not succeeded yet");
+    if (c->n_erased == 0) return RSGPU_OK;
+    if (!out_d) return fail_msg(RSGPU_EINVAL, "NULL argument");
+    if ((c->k > 1 && surv_pitch < len) || (c->n_erased > 1 && out_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
+    if (n_stripes > 1 && (surv_stripe_pitch < len || out_stripe_pitch < len)) return fail_msg(RSGPU_EINVAL, "stripe pitch < len");
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    if ((rc = plan_apply_batch(c, c->dec_erased(), surv_d, surv_pitch, surv_stripe_pitch, out_d, out_pitch, out_stripe_pitch, len,
+                               n_stripes, (cudaStream_t)stream)) != RSGPU_OK)
+        return rc;
     return mark_decode_use(c, (cudaStream_t)stream);
 }
 

@@ -99,6 +99,23 @@ int rsgpu_encode(rsgpu_ctx *ctx, const uint8_t *data_d, size_t data_pitch,
                  uint8_t *parity_d, size_t parity_pitch, size_t len, void *stream);
 
 /*
+ * Encode a BATCH of n_stripes stripes of the same code in one call: fragment j of stripe s starts at
+ * data_d + s * data_stripe_pitch + j * data_pitch, parity row i of stripe s at parity_d +
+ * s * parity_stripe_pitch + i * parity_pitch (stripe-major and fragment-major batches are both instances
+ * of this).  When everything is 16-byte aligned the whole batch is ONE kernel launch per group of 8 parity
+ * rows, with the work spread evenly over the GPU whatever the stripe size -- small stripes (fragments of
+ * 64 KiB .. a few MiB) are otherwise bound by the per-launch cost.  Other geometries are coded stripe by
+ * stripe, same result.  No counterpart in the reference (one file per process run); SURVEY 8e "device-
+ * resident batches".  Asynchronous on `stream`.  rsgpu_decode_erased_batch is the same for the lost natives.
+ */
+int rsgpu_encode_batch(rsgpu_ctx *ctx, const uint8_t *data_d, size_t data_pitch, size_t data_stripe_pitch,
+                       uint8_t *parity_d, size_t parity_pitch, size_t parity_stripe_pitch,
+                       size_t len, size_t n_stripes, void *stream);
+int rsgpu_decode_erased_batch(rsgpu_ctx *ctx, const uint8_t *survivors_d, size_t survivors_pitch,
+                              size_t survivors_stripe_pitch, uint8_t *out_d, size_t out_pitch,
+                              size_t out_stripe_pitch, size_t len, size_t n_stripes, void *stream);
+
+/*
  * Encode with one destination pointer per parity row (host array of p device pointers).  The rows may
  * be memory of OTHER GPUs of the box once rsgpu_enable_peer(ctx, that_device) has succeeded: the kernel's
  * 128-bit stores then travel over NVLink / NVSwitch while it computes the following columns, so the

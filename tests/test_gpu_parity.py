@@ -536,6 +536,77 @@ def test_batch_of_small_stripes_is_one_call(rs, orc, torch):
 
 # ---- per-row destinations, peer GPUs -----------------------------------------------------
 
+BATCH_CASES = [
+    # k, p, L, n_stripes, layout, variant
+    (10, 4, 65_536, 37, "stripe", 0), (10, 4, 65_536, 37, "fragment", 0), (16, 4, 4_096 * 16, 64, "stripe", 0),
+    (4, 2, 1 << 20, 5, "stripe", 0), (6, 3, 48_000, 19, "fragment", 0), (10, 8, 32_768, 21, "stripe", 0),
+    (12, 4, 160, 1000, "stripe", 5), (9, 3, 20_000 * 16, 3, "stripe", 0), (20, 4, 16_384, 33, "stripe", 0),
+    (10, 12, 16_384, 9, "stripe", 0),          # two row groups (8 + 4 rows): one batch launch each
+    (7, 3, 65_536, 11, "stripe", 0),           # no batch instance for k = 7: stripe-by-stripe fallback
+    (10, 4, 10_007, 13, "stripe", 0),          # len not a multiple of 16: fallback
+    (10, 4, 65_536, 1, "stripe", 0), (10, 4, 256, 3, "stripe", 0),
+]
+
+
+def _batch_views(torch, k, rows, L, n, layout, fill):
+    """device buffer + (row pitch, stripe pitch) for a batch of n stripes of `rows` rows of L bytes"""
+    Lp = (L + 255) // 256 * 256
+    if layout == "stripe":      # [stripe][row][Lp]
+        pitch, spitch = Lp, rows * Lp + 512
+    else:                       # [row][stripe][Lp]: rows of ALL stripes side by side
+        pitch, spitch = n * Lp + 256, Lp
+    size = (n - 1) * spitch + (rows - 1) * pitch + Lp if layout == "stripe" else rows * pitch
+    buf = torch.full((size + 64,), fill, dtype=torch.uint8, device="cuda")
+    return buf, pitch, spitch
+
+
+@pytest.mark.parametrize("k,p,L,n,layout,variant", BATCH_CASES)
+def test_encode_batch_vs_oracle(rs, orc, torch, k, p, L, n, layout, variant):
+    data = splitmix64_bytes(9000 + k + n, n * k * L).reshape(n, k, L)
+    din, dpitch, dsp = _batch_views(torch, k, k, L, n, layout, 0)
+    dout, ppitch, psp = _batch_views(torch, k, p, L, n, layout, 0xEE)
+    for s in range(n):
+        for j in range(k):
+            o = s * dsp + j * dpitch
+            din[o:o + L] = to_dev(torch, data[s, j])
+    with rs.RSContext(k, p) as ctx:
+        ctx.set_tuning(variant=variant)
+        n0 = ctx.launch_count()
+        ctx.encode_batch(din.data_ptr(), dpitch, dsp, dout.data_ptr(), ppitch, psp, L, n, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        launches = ctx.launch_count() - n0
+    V = orc.gen_encoding_matrix(p, k)
+    host = dout.cpu().numpy()
+    for s in range(n):
+        want = orc.matrix_mul(V, data[s])
+        for i in range(p):
+            o = s * psp + i * ppitch
+            assert (host[o:o + L] == want[i]).all(), f"stripe {s} parity {i}"
+    if L % 16 == 0 and n > 1 and k != 7 and (variant == 5 or L * n >= 2 << 20):
+        assert launches == (p + 7) // 8, "an aligned batch is one launch per group of 8 parity rows"
+
+
+def test_decode_erased_batch_roundtrip(rs, torch):
+    k, p, L, n = 10, 4, 96 * 1024, 29
+    stream = torch.cuda.current_stream().cuda_stream
+    data = torch.randint(0, 256, (n, k, L), dtype=torch.uint8, device="cuda")
+    parity = torch.empty((n, p, L), dtype=torch.uint8, device="cuda")
+    order = [10, 1, 11, 3, 12, 5, 6, 13, 8, 9]            # natives 0, 2, 4, 7 lost
+    with rs.RSContext(k, p) as ctx:
+        ctx.encode_batch(data.data_ptr(), L, k * L, parity.data_ptr(), L, p * L, L, n, stream)
+        frags = torch.cat([data, parity], dim=1)                          # (n, k+p, L)
+        surv = frags[:, torch.tensor(order, device="cuda")].contiguous()  # (n, k, L)
+        ctx.set_survivors(order)
+        er = ctx.erased()
+        assert er == [0, 2, 4, 7]
+        out = torch.empty((n, len(er), L), dtype=torch.uint8, device="cuda")
+        n0 = ctx.launch_count()
+        ctx.decode_erased_batch(surv.data_ptr(), L, k * L, out.data_ptr(), L, len(er) * L, L, n, stream)
+        torch.cuda.synchronize()
+        assert ctx.launch_count() - n0 == 1
+    assert torch.equal(out, data[:, torch.tensor(er, device="cuda")])
+
+
 @pytest.mark.parametrize("k,p,L", [(10, 4, 100_000 + 16), (16, 4, 65_536 + 7), (7, 3, 33_333), (32, 8, 40_000), (5, 6, 4096)])
 def test_encode_rows_same_device(rs, orc, torch, k, p, L):
     data = splitmix64_bytes(8100 + k, k * L).reshape(k, L)

@@ -2,7 +2,7 @@
 """BASELINE configs[3] at its full size: a batch of 64 RS(16,20) stripes of
 16 x 64 MiB (64 GiB of input + 16 GiB of parity), all device resident, GPU g owning the stripes
 s = g (mod G) -- strong scaling, no exchange between GPUs.  One step = one pass over the whole batch
-(one launch per stripe).  G = 1 keeps all 80 GiB on the one GPU (fits 180 GB; no half-batches).
+(one rsgpu_encode_batch launch per GPU; --per-stripe: one launch per stripe).  G = 1 keeps all 80 GiB on the one GPU (fits 180 GB; no half-batches).
 
     python tools/c4_batch.py                                   # 1 GPU
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--frag-mib", type=int, default=64)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--per-stripe", action="store_true", help="one rsgpu_encode launch per stripe instead of one batch call")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -53,8 +54,11 @@ def main():
     ctx = rs.RSContext(k, p, device=local)
 
     def step():
-        for i in range(len(mine)):
-            ctx.encode(data[i].data_ptr(), L, parity[i].data_ptr(), L, L, stream)
+        if args.per_stripe:
+            for i in range(len(mine)):
+                ctx.encode(data[i].data_ptr(), L, parity[i].data_ptr(), L, L, stream)
+        elif mine:      # the rank's stripes in ONE launch (rsgpu_encode_batch, stripe-major layout)
+            ctx.encode_batch(data.data_ptr(), L, k * L, parity.data_ptr(), L, p * L, L, len(mine), stream)
 
     def barrier():
         if world > 1:
@@ -108,7 +112,7 @@ def main():
                                    % (args.stripes, args.frag_mib), "input_bytes": in_bytes,
                        "resident_bytes_per_gpu": len(mine) * (k + p) * L, "self_check": "ok" if int(okt.item()) else "MISMATCH"},
             "roofline": {"bound": "hbm", "achieved": per_gpu_traffic, "peak": peak, "unit": "GB/s", "frac": per_gpu_traffic / peak,
-                         "note": "rank 0's stripes, whole step (launch gaps included)"},
+                         "note": "rank 0's stripes, whole step; " + ("one launch per stripe" if args.per_stripe else "one batch launch")},
             "gpu_launches": launches * world}), flush=True)
     if world > 1:
         dist.barrier()
