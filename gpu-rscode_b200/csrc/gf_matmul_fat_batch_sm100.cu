@@ -151,7 +151,8 @@ FatBatchKernel make_fat_batch()
     return FatBatchKernel{k_gf_matmul_fat_batch<W, JB, KB, PF, T7>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
 }
 
-// the batch shapes of gf_matmul_fat_sm100.cu (pick_fat) for the codes a batch of small stripes is likely to use
+// the batch shapes of gf_matmul_fat_sm100.cu (pick_fat); k that borrow a larger instance there (17, 19, ...) are
+// coded stripe by stripe
 template <int W>
 bool pick_fat_batch(int k, FatBatchKernel *fk)
 {
@@ -161,13 +162,20 @@ bool pick_fat_batch(int k, FatBatchKernel *fk)
     case 4: *fk = make_fat_batch<W, 4, 1>(); return true;
     case 5: *fk = make_fat_batch<W, 5, 1>(); return true;
     case 6: *fk = make_fat_batch<W, 6, 1>(); return true;
+    case 7: *fk = make_fat_batch<W, 7, 1>(); return true;
     case 8: *fk = make_fat_batch<W, 4, 2>(); return true;
     case 9: *fk = make_fat_batch<W, 3, 3>(); return true;
     case 10: *fk = make_fat_batch<W, 5, 2>(); return true;
+    case 11: *fk = make_fat_batch<W, 11, 1>(); return true;
     case 12: *fk = make_fat_batch<W, 3, 4>(); return true;
+    case 13: *fk = make_fat_batch<W, 13, 1>(); return true;
     case 14: *fk = make_fat_batch<W, 7, 2>(); return true;
+    case 15: *fk = make_fat_batch<W, 5, 3>(); return true;
     case 16: *fk = make_fat_batch<W, 4, 4>(); return true;
+    case 18: *fk = make_fat_batch<W, 3, 6>(); return true;
     case 20: *fk = make_fat_batch<W, 5, 4>(); return true;
+    case 24: *fk = make_fat_batch<W, 4, 6>(); return true;
+    case 32: *fk = make_fat_batch<W, 4, 8>(); return true;
     default: return false;
     }
 }
