@@ -522,6 +522,39 @@ def test_fuzz_encode_shapes_vs_oracle(rs, orc, torch):
     run()
 
 
+def test_fuzz_encode_batch_vs_per_stripe_calls(rs, orc, torch):
+    """Random batch geometries: the one-call result must equal rsgpu_encode stripe by stripe (itself checked
+    against the oracle above), and stripe 0 is checked against the oracle directly."""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=40, deadline=None, derandomize=True, suppress_health_check=list(HealthCheck))
+    @given(k=st.integers(1, 34), p=st.integers(1, 10), cols=st.integers(1, 3000), n=st.integers(1, 40),
+           tail=st.sampled_from([0, 0, 0, 5]), layout=st.sampled_from(["stripe", "fragment"]),
+           variant=st.sampled_from([0, 5, 5, 6]), seed=st.integers(0, 2**31))
+    def run(k, p, cols, n, tail, layout, variant, seed):
+        L = cols * 16 + tail
+        stream = torch.cuda.current_stream().cuda_stream
+        gen = torch.Generator(device="cuda").manual_seed(seed)
+        din, dpitch, dsp = _batch_views(torch, k, k, L, n, layout, 0)
+        din.random_(0, 256, generator=gen)
+        out_a, ppitch, psp = _batch_views(torch, k, p, L, n, layout, 0xEE)
+        out_b, _, _ = _batch_views(torch, k, p, L, n, layout, 0xEE)
+        with rs.RSContext(k, p) as ctx:
+            ctx.set_tuning(variant=variant)
+            ctx.encode_batch(din.data_ptr(), dpitch, dsp, out_a.data_ptr(), ppitch, psp, L, n, stream)
+            for s in range(n):
+                ctx.encode(din.data_ptr() + s * dsp, dpitch, out_b.data_ptr() + s * psp, ppitch, L, stream)
+            torch.cuda.synchronize()
+        assert torch.equal(out_a, out_b), (k, p, L, n, layout, variant)    # untouched gaps (0xEE) included
+        host_in, host_out = din.cpu().numpy(), out_a.cpu().numpy()
+        d0 = np.stack([host_in[j * dpitch:j * dpitch + L] for j in range(k)])
+        want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), d0)
+        for i in range(p):
+            assert (host_out[i * ppitch:i * ppitch + L] == want[i]).all(), (k, p, L, n, layout, variant, i)
+
+    run()
+
+
 def test_batch_of_small_stripes_is_one_call(rs, orc, torch):
     """include/rsgpu.h: stripes stored fragment-major side by side are ONE encode of len = stripes * L."""
     k, p, L, n = 10, 4, 64 * 1024, 24
