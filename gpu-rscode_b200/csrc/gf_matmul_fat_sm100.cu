@@ -151,7 +151,7 @@ bool pick_fat(int k, FatKernel *fk)
     case 11: *fk = make_fat<W, 11, 1>(); return true;
     case 13: *fk = make_fat<W, 13, 1>(); return true;
     case 9: *fk = make_fat<W, 3, 3>(); return true;
-    case 15: *fk = make_fat<W, 5, 3>(); return true;
+    case 15: *fk = make_fat<W, 4, 4, true>(); return true;   // on the k = 16 shape
     case 18: *fk = make_fat<W, 3, 6>(); return true;
     case 8: *fk = make_fat<W, 4, 2>(); return true;
     case 10: *fk = make_fat<W, 5, 2>(); return true;
