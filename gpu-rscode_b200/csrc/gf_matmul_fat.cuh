@@ -294,6 +294,26 @@ __device__ __forceinline__ void build_block_tables(uint32_t tb, const uint32_t *
     }
 }
 
+// Batch shape per k: X(k, JB fragments per batch, KB batches, PAD).  Measured on B200 (tools/sweep.py):
+//   * batches of 4 with 768 threads beat batches of 8 with 512 (RS(16,20): 0.888 vs 0.794 of the HBM peak,
+//     RS(8,12): 0.898 vs 0.816);
+//   * an EVEN batch count matters more than the batch size: with an odd one the two register buffers swap
+//     roles per column, the loop is unrolled over two columns and spills (same box, with the L2 prefetch:
+//     RS(10,14) 2x5 0.944 vs 5x2 1.005; RS(12,16) 4x3 0.890 vs 3x4 0.989 of the measured copy peak);
+//   * hence PAD = true: k without an even shape of its own runs on the next larger one with all-zero tables
+//     for the missing fragments (their loads are skipped) -- a few wasted lookups, still one lookup per real
+//     input byte.  Single-batch shape -> padded even shape, same box: RS(7,10) 0.822 -> 1.000, RS(11,15)
+//     0.937 -> 1.003, RS(13,17) 0.749 -> 0.964, RS(5,8) 0.914 -> 0.972, RS(15,20) 5x3 0.507 -> 0.623;
+//     nibble kernel -> padded shape: RS(17,20) 0.654 -> 0.842, RS(19,23) 0.667 -> 0.831, RS(23,27) 0.656 -> 0.762
+//     (k = 28 on the 32 shape loses, 0.633 vs 0.674, so 25..29 stay on the nibble kernels).
+//     k = 2, 3, 6 were tried on even shapes too: within noise of their single-batch shapes, left alone.
+#define RSGPU_FAT_SHAPES(X)                                                                                   \
+    X(2, 2, 1, false) X(3, 3, 1, false) X(4, 4, 1, false) X(5, 3, 2, true) X(6, 6, 1, false) X(7, 4, 2, true) \
+    X(8, 4, 2, false) X(9, 3, 3, false) X(10, 5, 2, false) X(11, 3, 4, true) X(12, 3, 4, false)               \
+    X(13, 7, 2, true) X(14, 7, 2, false) X(15, 4, 4, true) X(16, 4, 4, false) X(17, 3, 6, true)               \
+    X(18, 3, 6, false) X(19, 5, 4, true) X(20, 5, 4, false) X(21, 4, 6, true) X(22, 4, 6, true)               \
+    X(23, 4, 6, true) X(24, 4, 6, false) X(30, 4, 8, true) X(31, 4, 8, true) X(32, 4, 8, false)
+
 // which instances use the L2 prefetch / the transposed bit-7 accumulation (measurements: make_fat)
 __host__ __device__ constexpr bool fat_use_prefetch(int K) { return K >= 8; }
 __host__ __device__ constexpr bool fat_use_t7(int W, int K)

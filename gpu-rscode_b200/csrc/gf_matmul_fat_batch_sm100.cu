@@ -45,33 +45,33 @@ __device__ __forceinline__ size_t out_off(const Pos &p, const BatchGeom &g) { re
 
 // As ColumnBatches of gf_matmul_fat_sm100.cu, with the next column given as a pointer (nullptr = none) and the
 // prefetch distances as 64-bit byte deltas (the next column may sit in another stripe).
-template <int W, int K, int JB, int KB, int B, int SP, bool PF, bool T7>
+template <int W, int K, int JB, int KB, int B, int SP, bool PF, bool T7, bool PAD>
 struct ColumnBatchesB {
     __device__ __forceinline__ static void run(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
                                                const uint8_t *q_next, uint32_t lane_base, uint32_t tb, Acc<W> &acc,
-                                               ptrdiff_t pf0, ptrdiff_t pf1)
+                                               ptrdiff_t pf0, ptrdiff_t pf1, int k)
     {
         constexpr int PAR = (SP + B) & 1;
         uint4 (&cur)[JB] = PAR ? buf1 : buf0;
         uint4 (&nxt)[JB] = PAR ? buf0 : buf1;
         if constexpr (B + 1 < KB) {
-            load_batch<JB, PF, false, (B + 1) * JB>(nxt, q, in_pitch, pf0, K);
+            load_batch<JB, PF, PAD, (B + 1) * JB>(nxt, q, in_pitch, pf0, k);
         } else {
             if (q_next) {
                 q = q_next;
-                load_batch<JB, PF, false, 0>(nxt, q, in_pitch, pf1, K);
+                load_batch<JB, PF, PAD, 0>(nxt, q, in_pitch, pf1, k);
             }
         }
         BatchMac<W, K, JB, B, 0, T7>::run(cur, lane_base, tb, acc);
         if constexpr (B + 1 < KB)
-            ColumnBatchesB<W, K, JB, KB, B + 1, SP, PF, T7>::run(buf0, buf1, q, in_pitch, q_next, lane_base, tb, acc, pf0, pf1);
+            ColumnBatchesB<W, K, JB, KB, B + 1, SP, PF, T7, PAD>::run(buf0, buf1, q, in_pitch, q_next, lane_base, tb, acc, pf0, pf1, k);
     }
 };
 
-template <int W, int K, int JB, int KB, int SP, bool PF, bool T7>
+template <int W, int K, int JB, int KB, int SP, bool PF, bool T7, bool PAD>
 __device__ __forceinline__ void do_column_b(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
                                             const uint8_t *in, uint8_t *out, size_t out_pitch, const Pos &p, const Pos &pn,
-                                            const Pos &pnn, const BatchGeom &g, uint32_t lane_base, uint32_t tb, int nrows)
+                                            const Pos &pnn, const BatchGeom &g, uint32_t lane_base, uint32_t tb, int nrows, int k)
 {
     const bool has_n = valid(pn, g), has_nn = valid(pnn, g);
     const size_t o = in_off(p, g), on = in_off(pn, g);
@@ -86,7 +86,7 @@ __device__ __forceinline__ void do_column_b(uint4 (&buf0)[JB], uint4 (&buf1)[JB]
         if constexpr (W == 8) acc.b[i] = 0;
         else if constexpr (T7) acc.t[i] = 0;
     }
-    ColumnBatchesB<W, K, JB, KB, 0, SP, PF, T7>::run(buf0, buf1, q, in_pitch, has_n ? in + on : nullptr, lane_base, tb, acc, pf0, pf1);
+    ColumnBatchesB<W, K, JB, KB, 0, SP, PF, T7, PAD>::run(buf0, buf1, q, in_pitch, has_n ? in + on : nullptr, lane_base, tb, acc, pf0, pf1, k);
     const size_t oo = out_off(p, g);
     if constexpr (W == 8) {
         transpose_store(acc.a, out, out_pitch, oo, 0, nrows);
@@ -96,15 +96,15 @@ __device__ __forceinline__ void do_column_b(uint4 (&buf0)[JB], uint4 (&buf1)[JB]
     }
 }
 
-template <int W, int JB, int KB, bool PF, bool T7>
+template <int W, int JB, int KB, bool PF, bool T7, bool PAD>
 __global__ void __launch_bounds__(fat_threads(W, JB, T7), 1)
 k_gf_matmul_fat_batch(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
-                      const uint32_t *__restrict__ tab, int nrows, BatchGeom g)
+                      const uint32_t *__restrict__ tab, int nrows, BatchGeom g, int k)
 {
     constexpr int K = JB * KB;
     extern __shared__ __align__(16) uint8_t s_raw[];
     const uint32_t tb = ((uint32_t)__cvta_generic_to_shared(s_raw) + 255u) & ~255u;
-    build_block_tables<W, K, false>(tb, tab, K);
+    build_block_tables<W, K, PAD>(tb, tab, k);
     __syncthreads();
 
     const uint32_t lane = threadIdx.x & 31u;
@@ -118,16 +118,16 @@ k_gf_matmul_fat_batch(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *
     uint4 buf0[JB], buf1[JB];
     const uint8_t *q = in + in_off(p, g);
     if (valid(p, g))
-        load_batch<JB, PF, false, 0>(buf0, q, in_pitch, valid(pn, g) ? (ptrdiff_t)(in_off(pn, g) - in_off(p, g)) : (ptrdiff_t)0, K);
+        load_batch<JB, PF, PAD, 0>(buf0, q, in_pitch, valid(pn, g) ? (ptrdiff_t)(in_off(pn, g) - in_off(p, g)) : (ptrdiff_t)0, k);
 
     while (valid(p, g)) {
-        do_column_b<W, K, JB, KB, 0, PF, T7>(buf0, buf1, q, in_pitch, in, out, out_pitch, p, pn, pnn, g, lane_base, tb, nrows);
+        do_column_b<W, K, JB, KB, 0, PF, T7, PAD>(buf0, buf1, q, in_pitch, in, out, out_pitch, p, pn, pnn, g, lane_base, tb, nrows, k);
         p = pn;
         pn = pnn;
         advance(pnn, g);
         if constexpr (KB & 1) {          // odd batch count: the next column starts in the other buffer
             if (!valid(p, g)) break;
-            do_column_b<W, K, JB, KB, 1, PF, T7>(buf0, buf1, q, in_pitch, in, out, out_pitch, p, pn, pnn, g, lane_base, tb, nrows);
+            do_column_b<W, K, JB, KB, 1, PF, T7, PAD>(buf0, buf1, q, in_pitch, in, out, out_pitch, p, pn, pnn, g, lane_base, tb, nrows, k);
             p = pn;
             pn = pnn;
             advance(pnn, g);
@@ -135,7 +135,7 @@ k_gf_matmul_fat_batch(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *
     }
 }
 
-using FatBatchFn = void (*)(const uint8_t *, size_t, uint8_t *, size_t, const uint32_t *, int, BatchGeom);
+using FatBatchFn = void (*)(const uint8_t *, size_t, uint8_t *, size_t, const uint32_t *, int, BatchGeom, int);
 
 struct FatBatchKernel {
     FatBatchFn fn;
@@ -143,39 +143,22 @@ struct FatBatchKernel {
     int smem;
 };
 
-template <int W, int JB, int KB>
+template <int W, int JB, int KB, bool PAD>
 FatBatchKernel make_fat_batch()
 {
     constexpr int K = JB * KB;
     constexpr bool PF = fat_use_prefetch(K), T7 = fat_use_t7(W, K);
-    return FatBatchKernel{k_gf_matmul_fat_batch<W, JB, KB, PF, T7>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
+    return FatBatchKernel{k_gf_matmul_fat_batch<W, JB, KB, PF, T7, PAD>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
 }
 
-// the batch shapes of gf_matmul_fat_sm100.cu (pick_fat); k that borrow a larger instance there (17, 19, ...) are
-// coded stripe by stripe
+// the same shape per k as the single-stripe kernel (RSGPU_FAT_SHAPES, gf_matmul_fat.cuh)
 template <int W>
 bool pick_fat_batch(int k, FatBatchKernel *fk)
 {
     switch (k) {
-    case 2: *fk = make_fat_batch<W, 2, 1>(); return true;
-    case 3: *fk = make_fat_batch<W, 3, 1>(); return true;
-    case 4: *fk = make_fat_batch<W, 4, 1>(); return true;
-    case 5: *fk = make_fat_batch<W, 5, 1>(); return true;
-    case 6: *fk = make_fat_batch<W, 6, 1>(); return true;
-    case 7: *fk = make_fat_batch<W, 7, 1>(); return true;
-    case 8: *fk = make_fat_batch<W, 4, 2>(); return true;
-    case 9: *fk = make_fat_batch<W, 3, 3>(); return true;
-    case 10: *fk = make_fat_batch<W, 5, 2>(); return true;
-    case 11: *fk = make_fat_batch<W, 11, 1>(); return true;
-    case 12: *fk = make_fat_batch<W, 3, 4>(); return true;
-    case 13: *fk = make_fat_batch<W, 13, 1>(); return true;
-    case 14: *fk = make_fat_batch<W, 7, 2>(); return true;
-    case 15: *fk = make_fat_batch<W, 5, 3>(); return true;
-    case 16: *fk = make_fat_batch<W, 4, 4>(); return true;
-    case 18: *fk = make_fat_batch<W, 3, 6>(); return true;
-    case 20: *fk = make_fat_batch<W, 5, 4>(); return true;
-    case 24: *fk = make_fat_batch<W, 4, 6>(); return true;
-    case 32: *fk = make_fat_batch<W, 4, 8>(); return true;
+#define RSGPU_FAT_CASE(k_, jb_, kb_, pad_) case k_: *fk = make_fat_batch<W, jb_, kb_, pad_>(); return true;
+        RSGPU_FAT_SHAPES(RSGPU_FAT_CASE)
+#undef RSGPU_FAT_CASE
     default: return false;
     }
 }
@@ -209,7 +192,7 @@ cudaError_t launch_matmul_fat_batch(const RowGroup &g, int k, const uint8_t *in,
     geo.n_stripes = (uint32_t)n_stripes;
     geo.step_s = (uint32_t)(stride / nvec);
     geo.step_c = (uint32_t)(stride % nvec);
-    fk.fn<<<grid, fk.threads, fk.smem, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, g.nrows, geo);
+    fk.fn<<<grid, fk.threads, fk.smem, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, g.nrows, geo, k);
     return cudaGetLastError();
 }
 

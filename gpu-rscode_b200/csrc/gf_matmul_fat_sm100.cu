@@ -133,43 +133,15 @@ FatKernel make_fat()
     return FatKernel{k_gf_matmul_fat<W, JB, KB, PF, T7, PAD>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
 }
 
-// Batch shape per k (JB fragments per batch x KB batches), measured on B200: batches of 4 with 768
-// threads beat batches of 8 with 512 (RS(16,20): 0.888 vs 0.794 of the HBM peak, RS(8,12): 0.898 vs 0.816);
-// An even batch count matters more than the batch size: an odd one makes the two register buffers swap
-// roles per column, the loop is unrolled over two columns and spills (same box, with the L2 prefetch:
-// RS(10,14) 2x5 0.944 vs 5x2 1.005; RS(12,16) 4x3 0.890 vs 3x4 0.989 of the measured copy peak).
 template <int W>
 bool pick_fat(int k, FatKernel *fk)
 {
     switch (k) {
-    case 2: *fk = make_fat<W, 2, 1>(); return true;
-    case 3: *fk = make_fat<W, 3, 1>(); return true;
-    case 4: *fk = make_fat<W, 4, 1>(); return true;
-    case 5: *fk = make_fat<W, 5, 1>(); return true;
-    case 6: *fk = make_fat<W, 6, 1>(); return true;
-    case 7: *fk = make_fat<W, 7, 1>(); return true;
-    case 11: *fk = make_fat<W, 11, 1>(); return true;
-    case 13: *fk = make_fat<W, 13, 1>(); return true;
-    case 9: *fk = make_fat<W, 3, 3>(); return true;
-    case 15: *fk = make_fat<W, 4, 4, true>(); return true;   // on the k = 16 shape
-    case 18: *fk = make_fat<W, 3, 6>(); return true;
-    case 8: *fk = make_fat<W, 4, 2>(); return true;
-    case 10: *fk = make_fat<W, 5, 2>(); return true;
-    case 12: *fk = make_fat<W, 3, 4>(); return true;
-    case 14: *fk = make_fat<W, 7, 2>(); return true;
-    case 16: *fk = make_fat<W, 4, 4>(); return true;
-    case 20: *fk = make_fat<W, 5, 4>(); return true;
-    case 24: *fk = make_fat<W, 4, 6>(); return true;
-    case 32: *fk = make_fat<W, 4, 8>(); return true;
-    default: break;
+#define RSGPU_FAT_CASE(k_, jb_, kb_, pad_) case k_: *fk = make_fat<W, jb_, kb_, pad_>(); return true;
+        RSGPU_FAT_SHAPES(RSGPU_FAT_CASE)
+#undef RSGPU_FAT_CASE
+    default: return false;
     }
-    // k without an instance of its own runs on the next larger one with all-zero tables for the missing
-    // fragments (their loads are skipped): a few wasted lookups, still one lookup per real input byte
-    if (k == 17) { *fk = make_fat<W, 3, 6, true>(); return true; }
-    if (k == 19) { *fk = make_fat<W, 5, 4, true>(); return true; }
-    if (k >= 21 && k <= 23) { *fk = make_fat<W, 4, 6, true>(); return true; }
-    if (k >= 30 && k <= 31) { *fk = make_fat<W, 4, 8, true>(); return true; }   // k = 28: 0.633 vs 0.674 split-nibble
-    return false;
 }
 
 }  // namespace
