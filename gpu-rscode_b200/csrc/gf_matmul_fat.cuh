@@ -10,17 +10,17 @@ namespace {
 
 constexpr int kSmemBudget = 232448 - 256 - 1024 - 64;   // 227 KiB opt-in limit minus alignment slack and the two bit-7 constant areas (32 B per fragment, k <= 32)
 
-__host__ __device__ constexpr int fat_count(int k)
+__host__ __device__ constexpr int fat_count(int k, int xb = 0)
 {
     // every fragment wants at least a fat7 table (16 KiB); thin pages (256 B) for the rest
     int n = k;
-    while (n > 0 && n * 16384 + (k - n) * 256 > kSmemBudget) --n;
+    while (n > 0 && n * 16384 + (k - n) * 256 > kSmemBudget - xb) --n;
     return n;
 }
-__host__ __device__ constexpr int fat8_count(int k)
+__host__ __device__ constexpr int fat8_count(int k, int xb = 0)
 {
-    const int n = fat_count(k);
-    int left = kSmemBudget - n * 16384 - (k - n) * 256;
+    const int n = fat_count(k, xb);
+    int left = kSmemBudget - xb - n * 16384 - (k - n) * 256;
     int n8 = left / 16384;
     return n8 > n ? n : n8;
 }
@@ -77,25 +77,26 @@ template <> struct Acc<8> { uint32_t a[16]; uint32_t b[16]; };
 //   fragments [N8, NF)       fat7 tables, 16 KiB each
 //   fragments [NF, K)        split-nibble pages, 256 B each
 //   then K * 16 bytes: the product of 0x80 with every coefficient (bit-7 term of the fat7 fragments)
-template <int K> struct Map {
-    static constexpr int NF = fat_count(K);
-    static constexpr int N8 = fat8_count(K);
+// XB: bytes of the shared-memory window kept free for other uses (the cluster kernel's exchange buffers)
+template <int K, int XB = 0> struct Map {
+    static constexpr int NF = fat_count(K, XB);
+    static constexpr int N8 = fat8_count(K, XB);
     static constexpr int THIN0 = N8 * 32768 + (NF - N8) * 16384;
     static constexpr int C7 = THIN0 + (K - NF) * 256;
     static constexpr int C7R = C7 + K * 16;    // the same products, one output row per word, byte-replicated
     static constexpr int BYTES = C7R + K * 16;
-    static_assert(BYTES + 256 <= 232448, "shared-memory plan exceeds the 227 KiB opt-in limit");
+    static_assert(BYTES + XB + 256 <= 232448, "shared-memory plan exceeds the 227 KiB opt-in limit");
     __host__ __device__ static constexpr int off(int j)
     {
         return j < N8 ? j * 32768 : (j < NF ? N8 * 32768 + (j - N8) * 16384 : THIN0 + (j - NF) * 256);
     }
 };
 
-template <int W, int K, int J, bool T7>
+template <int W, int K, int J, bool T7, int XB = 0>
 __device__ __forceinline__ void mac_word(uint32_t w, uint32_t lane_base, uint32_t tb, uint32_t c7a, uint32_t c7b,
                                          Acc<W> &acc, int pos0)
 {
-    using M = Map<K>;
+    using M = Map<K, XB>;
     constexpr int OFF = M::off(J);
     if constexpr (J < M::NF) {
         constexpr bool F7 = (J >= M::N8);
@@ -143,10 +144,10 @@ __device__ __forceinline__ void mac_word(uint32_t w, uint32_t lane_base, uint32_
     }
 }
 
-template <int W, int K, int J, bool T7>
+template <int W, int K, int J, bool T7, int XB = 0>
 __device__ __forceinline__ void mac_vec(const uint4 &d, uint32_t lane_base, uint32_t tb, Acc<W> &acc)
 {
-    using M = Map<K>;
+    using M = Map<K, XB>;
     uint32_t c7a = 0, c7b = 0;
     if constexpr (J >= M::N8 && J < M::NF) {   // fat7: the bit-7 term
         if constexpr (!T7) {
@@ -171,19 +172,19 @@ __device__ __forceinline__ void mac_vec(const uint4 &d, uint32_t lane_base, uint
             }
         }
     }
-    mac_word<W, K, J, T7>(d.x, lane_base, tb, c7a, c7b, acc, 0);
-    mac_word<W, K, J, T7>(d.y, lane_base, tb, c7a, c7b, acc, 4);
-    mac_word<W, K, J, T7>(d.z, lane_base, tb, c7a, c7b, acc, 8);
-    mac_word<W, K, J, T7>(d.w, lane_base, tb, c7a, c7b, acc, 12);
+    mac_word<W, K, J, T7, XB>(d.x, lane_base, tb, c7a, c7b, acc, 0);
+    mac_word<W, K, J, T7, XB>(d.y, lane_base, tb, c7a, c7b, acc, 4);
+    mac_word<W, K, J, T7, XB>(d.z, lane_base, tb, c7a, c7b, acc, 8);
+    mac_word<W, K, J, T7, XB>(d.w, lane_base, tb, c7a, c7b, acc, 12);
 }
 
 // compile-time loop over the fragments of batch B
-template <int W, int K, int JB, int B, int JJ, bool T7>
+template <int W, int K, int JB, int B, int JJ, bool T7, int XB = 0>
 struct BatchMac {
     __device__ __forceinline__ static void run(const uint4 (&d)[JB], uint32_t lane_base, uint32_t tb, Acc<W> &acc)
     {
-        mac_vec<W, K, B * JB + JJ, T7>(d[JJ], lane_base, tb, acc);
-        if constexpr (JJ + 1 < JB) BatchMac<W, K, JB, B, JJ + 1, T7>::run(d, lane_base, tb, acc);
+        mac_vec<W, K, B * JB + JJ, T7, XB>(d[JJ], lane_base, tb, acc);
+        if constexpr (JJ + 1 < JB) BatchMac<W, K, JB, B, JJ + 1, T7, XB>::run(d, lane_base, tb, acc);
     }
 };
 
@@ -238,10 +239,10 @@ __device__ __forceinline__ void load_batch(uint4 (&d)[JB], const uint8_t *&q, si
 
 // Build the tables of this block from the 32-entry global tables (lo 16 + hi 16 per fragment); the caller
 // synchronises the block afterwards.
-template <int W, int K, bool PAD>
+template <int W, int K, bool PAD, int XB = 0>
 __device__ __forceinline__ void build_block_tables(uint32_t tb, const uint32_t *__restrict__ tab, int k)
 {
-    using M = Map<K>;
+    using M = Map<K, XB>;
     constexpr int WW = W / 4;            // words per entry
     constexpr int REP = 128 / W;         // replicas per entry: 32 (W=4) or 16 (W=8); one 128-byte row per x
     const int tid = threadIdx.x, nt = blockDim.x;

@@ -196,7 +196,20 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
     // is long enough to pay for building its tables (one 227 KiB fill per SM: measured break-even
     // on B200 at 4-8 MiB per fragment for RS(10,14)); 5 forces it, 6 forbids it
     bool done_vec = false;
-    if (nvec && (tune.variant == 5 || (tune.variant == 0 && len >= ((size_t)8 << 20)))) {
+    // variant 8: the cluster kernel for k = 17..32 (fragments split over two CTAs, partial parities exchanged
+    // through distributed shared memory).  Measured SLOWER than the single-CTA kernel on every such code
+    // (RS(24,28) 0.73 vs 0.81, RS(20,24) 0.67 vs 0.87, RS(32,36) 0.66 vs 0.71 of the HBM peak), so it is never
+    // chosen automatically; it stays as a tested, selectable experiment (DESIGN.md section 4.1 e)
+    if (nvec && tune.variant == 8) {
+        cudaError_t e = launch_matmul_fat_cluster(g, k, in, in_pitch, out_g, out_pitch, nvec, dev, tune.max_blocks, s);
+        if (e == cudaSuccess) {
+            done_vec = true;
+            if (launches) ++*launches;
+        } else if (e != cudaErrorNotSupported) {
+            return e;
+        }
+    }
+    if (nvec && !done_vec && (tune.variant == 5 || (tune.variant == 0 && len >= ((size_t)8 << 20)))) {
         cudaError_t e = launch_matmul_fat(g, k, in, in_pitch, out_g, out_pitch, nvec, dev, tune.max_blocks, tune.threads, s);
         if (e == cudaSuccess) {
             done_vec = true;

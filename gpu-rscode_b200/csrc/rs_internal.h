@@ -108,6 +108,12 @@ cudaError_t launch_matmul_fat_batch(const RowGroup &g, int k, const uint8_t *in,
                                     uint8_t *out_g, size_t out_pitch, size_t out_stripe, size_t nvec, size_t n_stripes,
                                     const DeviceInfo &dev, int max_blocks, cudaStream_t s);
 
+// ---- gf_matmul_fat_cluster_sm100.cu -------------------------------------------------------------
+// k = 17..32, at most 4 output rows: the fragments split over the two CTAs of a cluster, partial parities
+// exchanged through distributed shared memory.  cudaErrorNotSupported otherwise.
+cudaError_t launch_matmul_fat_cluster(const RowGroup &g, int k, const uint8_t *in, size_t in_pitch, uint8_t *out_g,
+                                      size_t out_pitch, size_t nvec, const DeviceInfo &dev, int max_blocks, cudaStream_t s);
+
 // ---- gf_matmul_rows_sm100.cu --------------------------------------------------------------------
 // One destination pointer per output row (rows may be peer-GPU memory: the stores go over NVLink).
 cudaError_t launch_matmul_rows(const RowGroup &g, int k, int kpad, const uint8_t *in, size_t in_pitch,

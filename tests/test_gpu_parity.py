@@ -148,6 +148,22 @@ def test_encode_bank_replicated_kernel_vs_oracle(rs, orc, torch, k, p):
     assert n_launch > 0
 
 
+@pytest.mark.parametrize("k", [17, 18, 20, 21, 23, 24, 25, 27, 28, 29, 31, 32])
+@pytest.mark.parametrize("p,L", [(4, 150_003), (3, 16 * 40), (1, 16 * 100_000), (2, 16 * 7 + 5), (4, 16 * 777_777)])
+def test_encode_cluster_kernel_vs_oracle(rs, orc, torch, k, p, L):
+    """variant 8 forces the 2-CTA cluster kernel (fragments split over the pair, partial parities exchanged
+    through distributed shared memory): ragged tails, stripes shorter than one warp, long stripes."""
+    if L > 16 * 200_000 and k not in (17, 24, 32):
+        pytest.skip("long stripe only for three k")
+    data = splitmix64_bytes(800 + k * 5 + p, k * L).reshape(k, L)
+    data[:, :min(L, 512)] = np.arange(512, dtype=np.uint8)[None, :min(L, 512)]
+    with rs.RSContext(k, p) as ctx:
+        ctx.set_tuning(variant=8)
+        pitch = (L + 255) // 256 * 256
+        got = gpu_encode(torch, ctx, data, pitch=pitch, out_pitch=pitch)
+    assert (got == orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)).all()
+
+
 def test_encode_pitch_and_misalignment(rs, orc, torch):
     k, p, L = 10, 4, 10_007
     data = splitmix64_bytes(5, k * L).reshape(k, L)
