@@ -51,3 +51,20 @@ def test_host_library_exports_reference_entry_points():
     H = ctypes.CDLL(rs.HOST_LIB_PATH)
     assert hasattr(H, "encode_file") and hasattr(H, "decode_file")
     assert os.access(rs.RS_BIN, os.X_OK)
+
+
+def test_c_example_links_against_header_and_library(tmp_path):
+    """examples/abi_example.c compiles with plain gcc against include/rsgpu.h and links with -lrsgpu; without a
+    GPU it must fail loudly (exit 1 with the CUDA error text), not compute anything on the CPU."""
+    import subprocess
+    import torch
+    if not os.path.exists(rs.LIB_PATH):
+        rs.build()
+    exe = str(tmp_path / "abi_example")
+    libdir = os.path.join(ROOT, "gpu-rscode_b200")
+    subprocess.run(["gcc", "-O2", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                    os.path.join(ROOT, "examples", "abi_example.c"), "-L", libdir, "-lrsgpu", "-Wl,-rpath," + libdir,
+                    "-o", exe], check=True)
+    if not torch.cuda.is_available():
+        r = subprocess.run([exe, "4096"], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 1 and "CUDA error" in r.stderr

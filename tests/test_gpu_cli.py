@@ -224,3 +224,16 @@ def test_cli_streaming_many_slabs_ring_reuse(rs_bin, tmp_path):
         for blk in iter(lambda: f.read(1 << 24), b""):
             h.update(blk)
     assert h.hexdigest() == want
+
+
+def test_c_example_builds_and_runs_through_the_abi(tmp_path):
+    """examples/abi_example.c: the ABI used from plain C (gcc, include/rsgpu.h, -lrsgpu), no Python between."""
+    from gpu_lib import ROOT
+    exe = str(tmp_path / "abi_example")
+    libdir = os.path.join(ROOT, "gpu-rscode_b200")
+    subprocess.run(["gcc", "-O2", "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "examples", "abi_example.c"),
+                    "-L", libdir, "-lrsgpu", "-Wl,-rpath," + libdir, "-o", exe], check=True)
+    for nbytes in ("1048576", "100003", "12582912"):       # aligned, ragged, long enough for the byte-table kernel
+        r = subprocess.run([exe, nbytes], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert "4 lost natives rebuilt, identical to the originals" in r.stdout
