@@ -109,6 +109,37 @@ k_gf_matmul_bytes(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__re
     }
 }
 
+// The same for the last (len % 16) bytes of every stripe of a batch: one thread per (stripe, byte).
+template <int W>
+__global__ void __launch_bounds__(256)
+k_gf_matmul_bytes_batch(const uint8_t *__restrict__ in, size_t in_pitch, size_t in_stripe, uint8_t *__restrict__ out,
+                        size_t out_pitch, size_t out_stripe, const uint32_t *__restrict__ tab, int k, int nrows, size_t c0,
+                        unsigned rem, size_t n_stripes)
+{
+    const size_t total = n_stripes * rem, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const size_t st = i / rem, c = c0 + (i - st * rem);
+        const uint8_t *src = in + st * in_stripe + c;
+        uint32_t a = 0, b = 0;
+        for (int j = 0; j < k; ++j) {
+            const unsigned x = src[(size_t)j * in_pitch];
+            const uint32_t *tl = tab + (size_t)j * 32 * (W / 4);
+            const uint32_t *th = tl + 16 * (W / 4);
+            if (W == 4) {
+                a ^= __ldg(tl + (x & 15u)) ^ __ldg(th + (x >> 4));
+            } else {
+                a ^= __ldg(tl + 2 * (x & 15u)) ^ __ldg(th + 2 * (x >> 4));
+                b ^= __ldg(tl + 2 * (x & 15u) + 1) ^ __ldg(th + 2 * (x >> 4) + 1);
+            }
+        }
+        uint8_t *dst = out + st * out_stripe + c;
+        for (int r = 0; r < nrows; ++r) {
+            const uint32_t wv = r < 4 ? a : b;
+            dst[(size_t)r * out_pitch] = (uint8_t)(wv >> (8 * (r & 3)));
+        }
+    }
+}
+
 using MatmulFn = void (*)(const uint8_t *, size_t, uint8_t *, size_t, const uint32_t *, int, int, int, int, size_t, uint32_t);
 
 template <int W, int EX>
@@ -265,6 +296,24 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
         if (launches) ++*launches;
     }
     return cudaSuccess;
+}
+
+// Bytes [c0, c0 + rem) of every stripe of a batch (rem = len % 16 <= 15) in one launch.
+cudaError_t launch_matmul_bytes_batch(const RowGroup &g, int k, const uint8_t *in, size_t in_pitch, size_t in_stripe,
+                                      uint8_t *out_g, size_t out_pitch, size_t out_stripe, size_t c0, unsigned rem,
+                                      size_t n_stripes, const DeviceInfo &dev, cudaStream_t s)
+{
+    if (rem == 0 || n_stripes == 0) return cudaSuccess;
+    size_t blocks = (n_stripes * rem + 255) / 256;
+    const size_t cap = (size_t)dev.sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    if (g.width == 4)
+        k_gf_matmul_bytes_batch<4><<<(unsigned)blocks, 256, 0, s>>>(in, in_pitch, in_stripe, out_g, out_pitch, out_stripe, g.d_tab, k,
+                                                                    g.nrows, c0, rem, n_stripes);
+    else
+        k_gf_matmul_bytes_batch<8><<<(unsigned)blocks, 256, 0, s>>>(in, in_pitch, in_stripe, out_g, out_pitch, out_stripe, g.d_tab, k,
+                                                                    g.nrows, c0, rem, n_stripes);
+    return cudaGetLastError();
 }
 
 }  // namespace rsgpu

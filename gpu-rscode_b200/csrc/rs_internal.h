@@ -108,6 +108,11 @@ cudaError_t launch_matmul_fat_batch(const RowGroup &g, int k, const uint8_t *in,
                                     uint8_t *out_g, size_t out_pitch, size_t out_stripe, size_t nvec, size_t n_stripes,
                                     const DeviceInfo &dev, int max_blocks, cudaStream_t s);
 
+// last (len % 16) bytes of every stripe of a batch, one launch (gf_matmul_sm100.cu)
+cudaError_t launch_matmul_bytes_batch(const RowGroup &g, int k, const uint8_t *in, size_t in_pitch, size_t in_stripe,
+                                      uint8_t *out_g, size_t out_pitch, size_t out_stripe, size_t c0, unsigned rem,
+                                      size_t n_stripes, const DeviceInfo &dev, cudaStream_t s);
+
 // ---- gf_matmul_fat_cluster_sm100.cu -------------------------------------------------------------
 // k = 17..32, at most 4 output rows: the fragments split over the two CTAs of a cluster, partial parities
 // exchanged through distributed shared memory.  cudaErrorNotSupported otherwise.

@@ -103,21 +103,31 @@ int plan_apply_batch(rsgpu_ctx *c, const Plan &pl, const uint8_t *in, size_t in_
 {
     if (!pl.valid) return fail_msg(RSGPU_ESTATE, "coding plan not built");
     if (len == 0 || n_stripes == 0) return RSGPU_OK;
-    const bool aligned = (((uintptr_t)in | (uintptr_t)out | in_pitch | out_pitch | in_stripe | out_stripe | len) & 15u) == 0;
-    const bool want = n_stripes > 1 && aligned && (c->tune.variant == 0 || c->tune.variant == 5) &&
+    // bases and pitches 16-byte aligned; len itself may be ragged: its last (len % 16) bytes per stripe go to one
+    // extra byte-granular launch over the whole batch
+    const bool aligned = (((uintptr_t)in | (uintptr_t)out | in_pitch | out_pitch | in_stripe | out_stripe) & 15u) == 0;
+    const bool want = n_stripes > 1 && aligned && len >= 16 && (c->tune.variant == 0 || c->tune.variant == 5) &&
                       (c->tune.variant == 5 || len * n_stripes >= ((size_t)2 << 20));
     if (want) {
         bool done = true;
+        const size_t nvec = len / 16;
+        const unsigned rem = (unsigned)(len - nvec * 16);
         for (int g = 0; g < pl.ngroups && done; ++g) {
             const RowGroup &rg = pl.grp[g];
-            cudaError_t e = launch_matmul_fat_batch(rg, pl.k, in, in_pitch, in_stripe, out + (size_t)rg.row0 * out_pitch, out_pitch,
-                                                    out_stripe, len / 16, n_stripes, c->dev, c->tune.max_blocks, s);
+            uint8_t *out_g = out + (size_t)rg.row0 * out_pitch;
+            cudaError_t e = launch_matmul_fat_batch(rg, pl.k, in, in_pitch, in_stripe, out_g, out_pitch, out_stripe, nvec, n_stripes,
+                                                    c->dev, c->tune.max_blocks, s);
             if (e == cudaErrorNotSupported) {
                 if (g != 0) return fail_msg(RSGPU_ECUDA, "batch kernel support differs between row groups");
                 done = false;   // no instance for this k: fall through to the per-stripe launches
-            } else if (e != cudaSuccess) {
-                return fail_cuda(e, "launch_matmul_fat_batch");
-            } else {
+                break;
+            }
+            if (e != cudaSuccess) return fail_cuda(e, "launch_matmul_fat_batch");
+            ++c->launches;
+            if (rem) {
+                e = launch_matmul_bytes_batch(rg, pl.k, in, in_pitch, in_stripe, out_g, out_pitch, out_stripe, nvec * 16, rem,
+                                              n_stripes, c->dev, s);
+                if (e != cudaSuccess) return fail_cuda(e, "launch_matmul_bytes_batch");
                 ++c->launches;
             }
         }

@@ -102,10 +102,11 @@ int rsgpu_encode(rsgpu_ctx *ctx, const uint8_t *data_d, size_t data_pitch,
  * Encode a BATCH of n_stripes stripes of the same code in one call: fragment j of stripe s starts at
  * data_d + s * data_stripe_pitch + j * data_pitch, parity row i of stripe s at parity_d +
  * s * parity_stripe_pitch + i * parity_pitch (stripe-major and fragment-major batches are both instances
- * of this).  When everything is 16-byte aligned the whole batch is ONE kernel launch per group of 8 parity
- * rows, with the work spread evenly over the GPU whatever the stripe size -- small stripes (fragments of
- * 64 KiB .. a few MiB) are otherwise bound by the per-launch cost.  Other geometries are coded stripe by
- * stripe, same result.  No counterpart in the reference (one file per process run); SURVEY 8e "device-
+ * of this).  When the bases, pitches and stripe pitches are 16-byte aligned the whole batch is ONE kernel
+ * launch per group of 8 parity rows (plus one small launch for the last len % 16 bytes of all stripes when
+ * len is ragged), with the work spread evenly over the GPU whatever the stripe size -- small stripes
+ * (fragments of 64 KiB .. a few MiB) are otherwise bound by the per-launch cost.  Other geometries are coded
+ * stripe by stripe, same result.  No counterpart in the reference (one file per process run); SURVEY 8e "device-
  * resident batches".  Asynchronous on `stream`.  rsgpu_decode_erased_batch is the same for the lost natives.
  */
 int rsgpu_encode_batch(rsgpu_ctx *ctx, const uint8_t *data_d, size_t data_pitch, size_t data_stripe_pitch,

@@ -594,7 +594,9 @@ BATCH_CASES = [
     (7, 3, 65_536, 33, "stripe", 0), (13, 4, 32_768, 17, "fragment", 0), (32, 8, 16_384, 9, "stripe", 0),
     (17, 3, 65_536, 11, "stripe", 0), (5, 2, 65_536, 40, "fragment", 0), (23, 4, 16_384, 16, "stripe", 0),   # padded shapes
     (25, 3, 65_536, 11, "stripe", 0),          # no byte-table instance for k = 25: stripe-by-stripe fallback
-    (10, 4, 10_007, 13, "stripe", 0),          # len not a multiple of 16: fallback
+    (10, 4, 10_007, 13, "stripe", 0),          # small ragged batch: stripe by stripe
+    (10, 4, 10_007, 13, "stripe", 5), (16, 4, 65_541, 40, "fragment", 0), (6, 7, 4_111, 50, "stripe", 5),   # ragged len: + one tail launch
+    (10, 4, 9, 100, "stripe", 5),              # shorter than one 16-byte column: stripe by stripe
     (10, 4, 65_536, 1, "stripe", 0), (10, 4, 256, 3, "stripe", 0),
 ]
 
@@ -633,8 +635,9 @@ def test_encode_batch_vs_oracle(rs, orc, torch, k, p, L, n, layout, variant):
         for i in range(p):
             o = s * psp + i * ppitch
             assert (host[o:o + L] == want[i]).all(), f"stripe {s} parity {i}"
-    if L % 16 == 0 and n > 1 and k != 25 and (variant == 5 or L * n >= 2 << 20):
-        assert launches == (p + 7) // 8, "an aligned batch is one launch per group of 8 parity rows"
+    if L >= 16 and n > 1 and k != 25 and (variant == 5 or L * n >= 2 << 20):
+        per_group = 1 if L % 16 == 0 else 2        # + one byte-granular launch for the ragged tails of all stripes
+        assert launches == per_group * ((p + 7) // 8), "an aligned batch is one launch per group of 8 parity rows"
 
 
 def test_decode_erased_batch_roundtrip(rs, torch):
