@@ -332,6 +332,39 @@ def main():
             c2 = s2.stop(tw0 + 0.5 * args.sustained_s, time.time())     # second half: settled clocks
             sustained["clocks"] = c2
 
+    # ---- small-stripe leg: the same bytes as a batch of stripes with 64 KiB fragments, ONE rsgpu_encode_batch
+    # call per step (stripe-major [stripe][fragment][64 KiB] inside the same buffers).  Not part of `value`. ----
+    batch_leg = None
+    if mode == "encode" and rank == 0 and L >= (1 << 20):
+        Ls = 64 << 10
+        n_st = (k * L) // (k * Ls)
+        flat_in, flat_out = data.view(-1), out.view(-1)
+
+        def batch_step():
+            ctx.encode_batch(flat_in, Ls, k * Ls, flat_out, Ls, p * Ls, Ls, n_st, stream)
+        for _ in range(3):
+            batch_step()
+        eb0, eb1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        nb = max(5, min(args.steps, 20))
+        l0 = ctx.launch_count()
+        eb0.record()
+        for _ in range(nb):
+            batch_step()
+        eb1.record()
+        torch.cuda.synchronize()
+        b_ms = eb0.elapsed_time(eb1) / nb
+        x = flat_in[:Ls].clone()
+        for j in range(1, k):
+            x ^= flat_in[j * Ls:(j + 1) * Ls]
+        batch_leg = {"fragment_bytes": Ls, "stripes_per_call": n_st, "ms_per_call": b_ms,
+                     "input_gbs": n_st * k * Ls / (b_ms / 1e3) / 1e9, "achieved": n_st * (k + p) * Ls / (b_ms / 1e3) / 1e9,
+                     "launches_per_call": (ctx.launch_count() - l0) // nb,
+                     "self_check": "ok" if bool((flat_out[:Ls] == x).all()) else "MISMATCH",
+                     "api": "rsgpu_encode_batch, stripe-major batch in the same device buffers"}
+        del x
+        step()                      # put the single-stripe parity back for the checks below
+        torch.cuda.synchronize()
+
     t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -420,6 +453,9 @@ def main():
     if sustained:
         sustained["frac"] = sustained["achieved"] / peak
         sustained["unit"] = "GB/s"
+    if batch_leg:
+        batch_leg["frac"] = batch_leg["achieved"] / peak
+        batch_leg["unit"] = "GB/s"
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "peak_source": peak_src, "kernel": "k_gf_matmul", "kernel_ms_mean": k_ms,
                 "kernel_ms_min": min(kernel_ms), "kernel_ms_median": statistics.median(kernel_ms),
@@ -459,6 +495,7 @@ def main():
         "gpu_launches": launches * n_gpus,
         "clocks": clocks,
         "sustained": sustained,
+        "batch_small_stripes": batch_leg,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
