@@ -518,6 +518,46 @@ def test_cauchy_generator_is_mds_and_roundtrips(rs, orc, torch):
         rs.RSContext(250, 10, generator="cauchy")          # k + p > 256
 
 
+def test_contexts_on_concurrent_host_threads(rs, orc, torch):
+    """include/rsgpu.h: one context per host thread.  Four threads, each with its own context, stream and code,
+    run encode + erased decode concurrently on the same GPU (ctypes drops the GIL during the calls)."""
+    import threading
+    codes = [(10, 4, 300_007), (16, 4, 200_000), (6, 3, 150_016), (32, 8, 40_000)]
+    errors = []
+
+    def work(idx):
+        try:
+            k, p, L = codes[idx]
+            data = splitmix64_bytes(31_000 + idx, k * L).reshape(k, L)
+            want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)
+            st = torch.cuda.Stream()
+            d = to_dev(torch, data)
+            par = torch.empty((p, L), dtype=torch.uint8, device="cuda")
+            lost = list(range(min(p, 3)))
+            order = list(range(k, k + len(lost))) + list(range(len(lost), k))
+            with rs.RSContext(k, p) as ctx:
+                for it in range(15):
+                    par.fill_(0xEE)
+                    ctx.encode(d, L, par, L, L, st.cuda_stream)
+                    st.synchronize()
+                    assert (par.cpu().numpy() == want).all(), (idx, it)
+                    ctx.set_survivors(order)
+                    surv = torch.cat([par[:len(lost)], d[len(lost):]]).contiguous()
+                    back = torch.empty((len(lost), L), dtype=torch.uint8, device="cuda")
+                    ctx.decode_erased(surv, L, back, L, L, st.cuda_stream)
+                    st.synchronize()
+                    assert torch.equal(back, d[:len(lost)]), (idx, it)
+        except Exception as e:          # noqa: BLE001 -- reported in the main thread
+            errors.append((idx, repr(e)))
+
+    ths = [threading.Thread(target=work, args=(i,)) for i in range(len(codes))]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not errors, errors
+
+
 # ---- randomized shapes (hypothesis): any k, p, length, pitch, misalignment, kernel variant -----------
 
 def test_fuzz_encode_shapes_vs_oracle(rs, orc, torch):
