@@ -62,6 +62,10 @@ cudaError_t launch_build_product_tables(const uint8_t *d_matrix, int k, int kpad
 
 // ---- gj_inverse.cu --------------------------------------------------------------------------
 // d_flag[0] = 0 ok, 1 singular.  d_in is not modified.  One block does the whole inversion.
+// gather + invert + tables of the full and the erased-rows plan in one launch (rsgpu_set_survivors)
+cudaError_t launch_decode_setup(const uint8_t *d_total, int k, int kpad, const int *survivors, const int *erased, int n_erased,
+                                uint8_t *d_inv, uint32_t *d_full_tabs, uint8_t *d_erased_matrix, uint32_t *d_erased_tabs,
+                                int *d_flag, const GfTables &gf, cudaStream_t s);
 cudaError_t launch_gj_invert(const uint8_t *d_in, uint8_t *d_inv, int n, int *d_flag,
                              const GfTables &gf, cudaStream_t s);
 

@@ -380,26 +380,20 @@ int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
     cudaStream_t s = c->setup_stream;
     CK(cudaStreamWaitEvent(s, ds.last_use, 0));   // the last decode that read this set's tables has finished
     if (!ds.full.d_matrix && (rc = plan_alloc(ds.full, k, k)) != RSGPU_OK) return rc;
-    CK(cudaMemcpyAsync(c->d_rows, idx, sizeof(int) * k, cudaMemcpyHostToDevice, s));
-    CK(launch_gather_rows(c->d_total, k, c->d_rows, k, c->d_sub, s));
-    CK(launch_gj_invert(c->d_sub, ds.full.d_matrix, k, c->d_flag, c->gf, s));
-    c->launches += 2;
+    if (c->n_erased > 0 && (ds.erased.rows != c->n_erased || !ds.erased.d_matrix))
+        if ((rc = plan_alloc(ds.erased, c->n_erased, k)) != RSGPU_OK) return rc;
+    // one launch: gather the survivor rows, invert, tables of the k x k plan, rows of the inverse that rebuild the
+    // erased natives and their tables (the index lists travel as kernel parameters)
+    CK(launch_decode_setup(c->d_total, k, ds.full.kpad, idx, c->erased, c->n_erased, ds.full.d_matrix, ds.full.d_tabs,
+                           c->n_erased > 0 ? ds.erased.d_matrix : nullptr, c->n_erased > 0 ? ds.erased.d_tabs : nullptr,
+                           c->d_flag, c->gf, s));
+    ++c->launches;
     int flag = 0;
     CK(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     if (flag) return fail_msg(RSGPU_ESINGULAR, "the chosen survivors give a singular matrix");
-    if ((rc = plan_build_tables(c, ds.full, s)) != RSGPU_OK) return rc;
-
-    if (c->n_erased > 0) {
-        if (ds.erased.rows != c->n_erased || !ds.erased.d_matrix)
-            if ((rc = plan_alloc(ds.erased, c->n_erased, k)) != RSGPU_OK) return rc;
-        // rows of the inverse that rebuild the erased natives
-        CK(cudaMemcpyAsync(c->d_rows, c->erased, sizeof(int) * c->n_erased, cudaMemcpyHostToDevice, s));
-        CK(launch_gather_rows(ds.full.d_matrix, k, c->d_rows, c->n_erased, ds.erased.d_matrix, s));
-        ++c->launches;
-        if ((rc = plan_build_tables(c, ds.erased, s)) != RSGPU_OK) return rc;
-    }
-    CK(cudaStreamSynchronize(s));
+    ds.full.valid = true;
+    if (c->n_erased > 0) ds.erased.valid = true;
     c->dec_cur ^= 1;
     c->have_survivors = true;
     return RSGPU_OK;
