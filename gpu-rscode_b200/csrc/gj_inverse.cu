@@ -199,7 +199,7 @@ k_decode_setup(const uint8_t *__restrict__ total, int k, int kpad, SetupLists li
         erased_matrix[i] = v;
     }
     __syncthreads();
-    build_tables_from_smem(R, n, n, kpad, full_tabs, ex, lg);
+    if (full_tabs) build_tables_from_smem(R, n, n, kpad, full_tabs, ex, lg);   // nullptr: built later, on first use
     if (n_erased > 0) build_tables_from_smem(A, n_erased, n, kpad, erased_tabs, ex, lg);
 }
 

@@ -129,6 +129,8 @@ int rsgpu_decode_host(rsgpu_ctx *c, const uint8_t *surv, size_t surv_pitch, uint
     if (c->k > 1 && (surv_pitch < len || natives_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
     int rc = ctx_bind(c);
     if (rc) return rc;
+    if ((rc = ensure_full_tables(c, c->setup_stream)) != RSGPU_OK) return rc;
+    CK(cudaStreamSynchronize(c->setup_stream));     // the slot streams do not wait on the set-up stream by themselves
     return pipeline_run(c, c->dec_full(), surv, surv_pitch, natives, natives_pitch, len, slots);
 }
 

@@ -59,4 +59,5 @@ int ctx_bind(const rsgpu_ctx *c);
 int plan_apply(rsgpu_ctx *c, const Plan &pl, const uint8_t *in, size_t in_pitch, uint8_t *out, size_t out_pitch,
                size_t len, cudaStream_t s);
 void pipeline_free(rsgpu_ctx *c);
+int ensure_full_tables(rsgpu_ctx *c, cudaStream_t s);
 }  // namespace rsgpu

@@ -140,6 +140,14 @@ int plan_apply_batch(rsgpu_ctx *c, const Plan &pl, const uint8_t *in, size_t in_
     return RSGPU_OK;
 }
 
+// Tables of the full k x k plan of the current decode set, built on `s` the first time they are needed.
+int ensure_full_tables(rsgpu_ctx *c, cudaStream_t s)
+{
+    Plan &pl = c->dec_full();
+    if (pl.valid) return RSGPU_OK;
+    return plan_build_tables(c, pl, s);
+}
+
 int ctx_bind(const rsgpu_ctx *c)
 {
     CK(cudaSetDevice(c->device));
@@ -384,7 +392,9 @@ int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
         if ((rc = plan_alloc(ds.erased, c->n_erased, k)) != RSGPU_OK) return rc;
     // one launch: gather the survivor rows, invert, tables of the k x k plan, rows of the inverse that rebuild the
     // erased natives and their tables (the index lists travel as kernel parameters)
-    CK(launch_decode_setup(c->d_total, k, ds.full.kpad, idx, c->erased, c->n_erased, ds.full.d_matrix, ds.full.d_tabs,
+    // the tables of the full k x k plan are only needed by the reference-semantic rsgpu_decode[_host]: they are
+    // built on its first use (ensure_full_tables), not here
+    CK(launch_decode_setup(c->d_total, k, ds.full.kpad, idx, c->erased, c->n_erased, ds.full.d_matrix, nullptr,
                            c->n_erased > 0 ? ds.erased.d_matrix : nullptr, c->n_erased > 0 ? ds.erased.d_tabs : nullptr,
                            c->d_flag, c->gf, s));
     ++c->launches;
@@ -392,7 +402,7 @@ int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
     CK(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     if (flag) return fail_msg(RSGPU_ESINGULAR, "the chosen survivors give a singular matrix");
-    ds.full.valid = true;
+    ds.full.valid = false;                        // matrix there, tables not yet
     if (c->n_erased > 0) ds.erased.valid = true;
     c->dec_cur ^= 1;
     c->have_survivors = true;
@@ -472,6 +482,7 @@ int rsgpu_decode(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, uint8_t
     if (c->k > 1 && (surv_pitch < len || nat_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
     int rc = ctx_bind(c);
     if (rc) return rc;
+    if ((rc = ensure_full_tables(c, (cudaStream_t)stream)) != RSGPU_OK) return rc;
     if ((rc = plan_apply(c, c->dec_full(), surv_d, surv_pitch, nat_d, nat_pitch, len, (cudaStream_t)stream)) != RSGPU_OK) return rc;
     return mark_decode_use(c, (cudaStream_t)stream);
 }
