@@ -302,6 +302,8 @@ DEC_CASES = [
     (32, 8, list(range(32, 40)) + list(range(8, 32)), 9_001),
     (5, 3, [7, 6, 5, 4, 3], 2_222),
     (10, 4, list(range(10)), 5_000),        # nothing erased
+    (200, 20, [200, 201, 202] + list(range(3, 200)), 4_096),    # large k: 1024-thread set-up kernel, 25 row groups
+    (255, 1, [255] + list(range(1, 255)), 2_048),
 ]
 
 
