@@ -19,39 +19,22 @@
 
 namespace rsgpu {
 
-__global__ void __launch_bounds__(1024, 1)
-k_gj_invert(const uint8_t *__restrict__ in, uint8_t *__restrict__ inv, int n, int *flag,
-            const uint8_t *__restrict__ gexp, const uint8_t *__restrict__ glog)
+// The elimination itself, shared by both kernels below.  A (n x n, the matrix) and R (n x n, starts as the
+// identity) are in shared memory, ex/lg the field tables, fac n bytes of staging, s_piv one shared int.
+// Returns false (for every thread) when a column has no pivot; on success R is the inverse and A the identity.
+// Five block barriers per column, no global traffic.
+__device__ __forceinline__ bool gauss_jordan_smem(uint8_t *A, uint8_t *R, int n, const uint8_t *ex, const uint8_t *lg,
+                                                  uint8_t *fac, int *s_piv)
 {
-    extern __shared__ uint8_t sm[];
-    uint8_t *A = sm;                  // n*n
-    uint8_t *R = A + n * n;           // n*n
-    uint8_t *ex = R + n * n;          // 512
-    uint8_t *lg = ex + kExpSize;      // 256
-    uint8_t *fac = lg + kLogSize;     // n : elimination factor of each row for the current column
-    __shared__ int s_piv;
-
     const int tid = threadIdx.x, nt = blockDim.x;
-    for (int i = tid; i < kExpSize; i += nt) ex[i] = gexp[i];
-    for (int i = tid; i < kLogSize; i += nt) lg[i] = glog[i];
-    for (int i = tid; i < n * n; i += nt) {
-        A[i] = in[i];
-        R[i] = (uint8_t)((i / n) == (i % n));
-    }
-    if (tid == 0) *flag = 0;
-    __syncthreads();
-
     for (int c = 0; c < n; ++c) {
-        if (tid == 0) s_piv = INT_MAX;
+        if (tid == 0) *s_piv = INT_MAX;
         __syncthreads();
         for (int r = c + tid; r < n; r += nt)
-            if (A[r * n + c]) atomicMin(&s_piv, r);
+            if (A[r * n + c]) atomicMin(s_piv, r);
         __syncthreads();
-        const int piv = s_piv;
-        if (piv == INT_MAX) {          // uniform: every thread read the same value
-            if (tid == 0) *flag = 1;
-            return;
-        }
+        const int piv = *s_piv;
+        if (piv == INT_MAX) return false;   // uniform: every thread read the same value
         if (piv != c) {
             for (int col = tid; col < 2 * n; col += nt) {
                 uint8_t *M = col < n ? A : R;
@@ -82,6 +65,35 @@ k_gj_invert(const uint8_t *__restrict__ in, uint8_t *__restrict__ inv, int n, in
             }
         }
         __syncthreads();
+    }
+    return true;
+}
+
+__global__ void __launch_bounds__(1024, 1)
+k_gj_invert(const uint8_t *__restrict__ in, uint8_t *__restrict__ inv, int n, int *flag,
+            const uint8_t *__restrict__ gexp, const uint8_t *__restrict__ glog)
+{
+    extern __shared__ uint8_t sm[];
+    uint8_t *A = sm;                  // n*n
+    uint8_t *R = A + n * n;           // n*n
+    uint8_t *ex = R + n * n;          // 512
+    uint8_t *lg = ex + kExpSize;      // 256
+    uint8_t *fac = lg + kLogSize;     // n : elimination factor of each row for the current column
+    __shared__ int s_piv;
+
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (int i = tid; i < kExpSize; i += nt) ex[i] = gexp[i];
+    for (int i = tid; i < kLogSize; i += nt) lg[i] = glog[i];
+    for (int i = tid; i < n * n; i += nt) {
+        A[i] = in[i];
+        R[i] = (uint8_t)((i / n) == (i % n));
+    }
+    if (tid == 0) *flag = 0;
+    __syncthreads();
+
+    if (!gauss_jordan_smem(A, R, n, ex, lg, fac, &s_piv)) {
+        if (tid == 0) *flag = 1;
+        return;
     }
     for (int i = tid; i < n * n; i += nt) inv[i] = R[i];
 }
@@ -149,46 +161,9 @@ k_decode_setup(const uint8_t *__restrict__ total, int k, int kpad, SetupLists li
     if (tid == 0) *flag = 0;
     __syncthreads();
 
-    for (int c = 0; c < n; ++c) {
-        if (tid == 0) s_piv = INT_MAX;
-        __syncthreads();
-        for (int r = c + tid; r < n; r += nt)
-            if (A[r * n + c]) atomicMin(&s_piv, r);
-        __syncthreads();
-        const int piv = s_piv;
-        if (piv == INT_MAX) {          // uniform
-            if (tid == 0) *flag = 1;
-            return;
-        }
-        if (piv != c) {
-            for (int col = tid; col < 2 * n; col += nt) {
-                uint8_t *M = col < n ? A : R;
-                const int cc = col < n ? col : col - n;
-                const uint8_t t = M[c * n + cc];
-                M[c * n + cc] = M[piv * n + cc];
-                M[piv * n + cc] = t;
-            }
-            __syncthreads();
-        }
-        const unsigned pinv = gf_inv(ex, lg, A[c * n + c]);
-        __syncthreads();
-        for (int col = tid; col < 2 * n; col += nt) {
-            uint8_t *M = col < n ? A : R;
-            const int cc = col < n ? col : col - n;
-            M[c * n + cc] = (uint8_t)gf_mul(ex, lg, M[c * n + cc], pinv);
-        }
-        for (int q = tid; q < n; q += nt) fac[q] = (q == c) ? 0 : A[q * n + c];
-        __syncthreads();
-        for (int idx = tid; idx < 2 * n * n; idx += nt) {
-            const int q = idx / (2 * n), col = idx - q * 2 * n;
-            const unsigned f = fac[q];
-            if (f) {
-                uint8_t *M = col < n ? A : R;
-                const int cc = col < n ? col : col - n;
-                M[q * n + cc] ^= (uint8_t)gf_mul(ex, lg, f, M[c * n + cc]);
-            }
-        }
-        __syncthreads();
+    if (!gauss_jordan_smem(A, R, n, ex, lg, fac, &s_piv)) {
+        if (tid == 0) *flag = 1;
+        return;
     }
     // R = inverse.  A is free now: reuse it for the rows of the erased natives.
     for (int i = tid; i < n * n; i += nt) inv[i] = R[i];

@@ -4,6 +4,22 @@
 
 constexpr int kMaxSlots = 16;
 
+// Which streams have kernels in flight that read a set of tables.  One event per distinct stream (up to
+// kSlots; a further stream is chained behind the oldest slot), so that whoever rebuilds the tables can wait
+// for ALL of them, not only for the stream that happened to be used last.
+struct UseTracker {
+    static constexpr int kSlots = 4;
+    cudaEvent_t ev[kSlots] = {};
+    cudaStream_t stream[kSlots] = {};
+    int n = 0;          // slots holding a recorded event
+    int victim = 0;     // next slot to take over when all are taken by other streams
+    cudaError_t create();
+    void destroy();
+    cudaError_t mark(cudaStream_t s);            // call after queueing a reader on s
+    cudaError_t wait_all(cudaStream_t writer);   // writer waits for every recorded reader
+    void reset() { n = 0; }                      // after the writer's stream has been synchronised
+};
+
 struct rsgpu_ctx {
     int device = 0;
     int k = 0, p = 0;
@@ -25,7 +41,8 @@ struct rsgpu_ctx {
     struct DecodeSet {
         rsgpu::Plan full;         // k x k inverse (reference-semantic decode)
         rsgpu::Plan erased;       // e x k rows of the inverse for the erased natives
-        cudaEvent_t last_use = nullptr;
+        UseTracker readers;            // decodes in flight on this set, per stream
+        cudaEvent_t full_ready = nullptr;   // recorded on setup_stream behind the lazily built tables of `full`
     };
     DecodeSet dec[2];
     int dec_cur = 0;
@@ -34,7 +51,8 @@ struct rsgpu_ctx {
     rsgpu::Plan scratch;          // rsgpu_matmul's caller-supplied matrix
     rsgpu::Plan repair;           // m x k: T[wanted] * inverse, rebuilds any wanted fragments
     bool have_repair = false;
-    cudaEvent_t repair_last_use = nullptr;   // same ordering for rsgpu_set_repair after rsgpu_repair
+    UseTracker repair_readers;    // same ordering for rsgpu_set_repair after rsgpu_repair
+    uint8_t *d_inv_scratch = nullptr;   // rsgpu_invert_matrix: 2 x 255 x 255 bytes, allocated on its first call, kept
 
     bool have_survivors = false;
     int survivors[256];

@@ -30,6 +30,56 @@ int fail_msg(int code, const char *msg)
     return code;
 }
 
+}  // namespace rsgpu
+
+cudaError_t UseTracker::create()
+{
+    for (auto &e : ev) {
+        cudaError_t r = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        if (r != cudaSuccess) return r;
+    }
+    return cudaSuccess;
+}
+
+void UseTracker::destroy()
+{
+    for (auto &e : ev)
+        if (e) {
+            cudaEventDestroy(e);
+            e = nullptr;
+        }
+    n = 0;
+}
+
+cudaError_t UseTracker::mark(cudaStream_t s)
+{
+    for (int i = 0; i < n; ++i)
+        if (stream[i] == s) return cudaEventRecord(ev[i], s);
+    if (n < kSlots) {
+        stream[n] = s;
+        return cudaEventRecord(ev[n++], s);
+    }
+    // more streams than slots: s takes over the oldest slot after waiting for what that slot covered, so the
+    // slot's new event still stands for both
+    const int i = victim;
+    victim = (victim + 1) % kSlots;
+    cudaError_t r = cudaStreamWaitEvent(s, ev[i], 0);
+    if (r != cudaSuccess) return r;
+    stream[i] = s;
+    return cudaEventRecord(ev[i], s);
+}
+
+cudaError_t UseTracker::wait_all(cudaStream_t writer)
+{
+    for (int i = 0; i < n; ++i) {
+        cudaError_t r = cudaStreamWaitEvent(writer, ev[i], 0);
+        if (r != cudaSuccess) return r;
+    }
+    return cudaSuccess;
+}
+
+namespace rsgpu {
+
 #define CK(call)                                                   \
     do {                                                           \
         cudaError_t e__ = (call);                                  \
@@ -140,12 +190,20 @@ int plan_apply_batch(rsgpu_ctx *c, const Plan &pl, const uint8_t *in, size_t in_
     return RSGPU_OK;
 }
 
-// Tables of the full k x k plan of the current decode set, built on `s` the first time they are needed.
+// Tables of the full k x k plan of the current decode set, built the first time they are needed -- on the
+// context's set-up stream, with an event behind them that EVERY caller's stream waits on: a second
+// rsgpu_decode on another stream must not start reading tables whose build is still queued on the first.
 int ensure_full_tables(rsgpu_ctx *c, cudaStream_t s)
 {
-    Plan &pl = c->dec_full();
-    if (pl.valid) return RSGPU_OK;
-    return plan_build_tables(c, pl, s);
+    rsgpu_ctx::DecodeSet &ds = c->dec[c->dec_cur];
+    Plan &pl = ds.full;
+    if (!pl.valid) {
+        int rc = plan_build_tables(c, pl, c->setup_stream);
+        if (rc != RSGPU_OK) return rc;
+        CK(cudaEventRecord(ds.full_ready, c->setup_stream));
+    }
+    if (s != c->setup_stream) CK(cudaStreamWaitEvent(s, ds.full_ready, 0));
+    return RSGPU_OK;
 }
 
 int ctx_bind(const rsgpu_ctx *c)
@@ -191,8 +249,10 @@ static int ctx_create(rsgpu_ctx **out, int device, int k, int p, const uint8_t *
     if ((e = cudaMalloc(&c->d_rows, sizeof(int) * 256)) != cudaSuccess) return bail(fail_cuda(e, "cudaMalloc row list"));
     if ((e = cudaMalloc(&c->d_flag, sizeof(int))) != cudaSuccess) return bail(fail_cuda(e, "cudaMalloc flag"));
 
-    for (cudaEvent_t *ev : {&c->dec[0].last_use, &c->dec[1].last_use, &c->repair_last_use})
+    for (cudaEvent_t *ev : {&c->dec[0].full_ready, &c->dec[1].full_ready})
         if ((e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming)) != cudaSuccess) return bail(fail_cuda(e, "cudaEventCreate"));
+    for (UseTracker *t : {&c->dec[0].readers, &c->dec[1].readers, &c->repair_readers})
+        if ((e = t->create()) != cudaSuccess) return bail(fail_cuda(e, "cudaEventCreate"));
 
     cudaStream_t s = c->setup_stream;
     if ((e = launch_build_gf_tables(c->gf.d_exp, c->gf.d_log, s)) != cudaSuccess) return bail(fail_cuda(e, "build_gf_tables"));
@@ -277,9 +337,11 @@ void rsgpu_destroy(rsgpu_ctx *c)
     for (auto &ds : c->dec) {
         plan_free(ds.full);
         plan_free(ds.erased);
-        if (ds.last_use) cudaEventDestroy(ds.last_use);
+        ds.readers.destroy();
+        if (ds.full_ready) cudaEventDestroy(ds.full_ready);
     }
-    if (c->repair_last_use) cudaEventDestroy(c->repair_last_use);
+    c->repair_readers.destroy();
+    if (c->d_inv_scratch) cudaFree(c->d_inv_scratch);
     plan_free(c->scratch);
     plan_free(c->repair);
     if (c->gf.d_exp) cudaFree(c->gf.d_exp);
@@ -386,7 +448,7 @@ int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
     memcpy(c->survivors, idx, sizeof(int) * k);
 
     cudaStream_t s = c->setup_stream;
-    CK(cudaStreamWaitEvent(s, ds.last_use, 0));   // the last decode that read this set's tables has finished
+    CK(ds.readers.wait_all(s));   // every decode that still reads this set's tables, on whatever stream, finishes first
     if (!ds.full.d_matrix && (rc = plan_alloc(ds.full, k, k)) != RSGPU_OK) return rc;
     if (c->n_erased > 0 && (ds.erased.rows != c->n_erased || !ds.erased.d_matrix))
         if ((rc = plan_alloc(ds.erased, c->n_erased, k)) != RSGPU_OK) return rc;
@@ -401,6 +463,7 @@ int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
     int flag = 0;
     CK(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
+    ds.readers.reset();                           // the set-up stream has drained: nobody reads the old tables any more
     if (flag) return fail_msg(RSGPU_ESINGULAR, "the chosen survivors give a singular matrix");
     ds.full.valid = false;                        // matrix there, tables not yet
     if (c->n_erased > 0) ds.erased.valid = true;
@@ -413,7 +476,7 @@ int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
 // in rsgpu_set_survivors.
 static int mark_decode_use(rsgpu_ctx *c, cudaStream_t s)
 {
-    CK(cudaEventRecord(c->dec[c->dec_cur].last_use, s));
+    CK(c->dec[c->dec_cur].readers.mark(s));
     return RSGPU_OK;
 }
 
@@ -428,7 +491,7 @@ int rsgpu_set_repair(rsgpu_ctx *c, const int *survivors, const int *wanted, int 
     if (rc != RSGPU_OK) return rc;
     const int k = c->k;
     cudaStream_t s = c->setup_stream;
-    CK(cudaStreamWaitEvent(s, c->repair_last_use, 0));   // the last rsgpu_repair has finished with the old tables
+    CK(c->repair_readers.wait_all(s));   // every rsgpu_repair still in flight has finished with the old tables
     if (c->repair.rows != n_wanted || !c->repair.d_matrix)
         if ((rc = plan_alloc(c->repair, n_wanted, k)) != RSGPU_OK) return rc;
     // repair matrix = (rows `wanted` of the total matrix) x inverse: natives come out as rows of the
@@ -438,6 +501,7 @@ int rsgpu_set_repair(rsgpu_ctx *c, const int *survivors, const int *wanted, int 
     ++c->launches;
     if ((rc = plan_build_tables(c, c->repair, s)) != RSGPU_OK) return rc;
     CK(cudaStreamSynchronize(s));
+    c->repair_readers.reset();
     c->have_repair = true;
     return RSGPU_OK;
 }
@@ -451,7 +515,7 @@ int rsgpu_repair(rsgpu_ctx *c, const uint8_t *surv_d, size_t surv_pitch, uint8_t
     int rc = ctx_bind(c);
     if (rc) return rc;
     if ((rc = plan_apply(c, c->repair, surv_d, surv_pitch, out_d, out_pitch, len, (cudaStream_t)stream)) != RSGPU_OK) return rc;
-    CK(cudaEventRecord(c->repair_last_use, (cudaStream_t)stream));
+    CK(c->repair_readers.mark((cudaStream_t)stream));
     return RSGPU_OK;
 }
 
@@ -524,8 +588,8 @@ int rsgpu_invert_matrix(rsgpu_ctx *c, const uint8_t *matrix, uint8_t *inverse, i
     if (n < 1 || n > 255) return fail_msg(RSGPU_EINVAL, "need 1 <= n <= 255");
     int rc = ctx_bind(c);
     if (rc) return rc;
-    uint8_t *d = nullptr;
-    CK(cudaMalloc(&d, (size_t)2 * n * n));
+    if (!c->d_inv_scratch) CK(cudaMalloc(&c->d_inv_scratch, (size_t)2 * 255 * 255));   // once per context, kept
+    uint8_t *d = c->d_inv_scratch;
     cudaStream_t s = c->setup_stream;
     int flag = 0;
     cudaError_t e = cudaMemcpyAsync(d, matrix, (size_t)n * n, cudaMemcpyHostToDevice, s);
@@ -533,7 +597,6 @@ int rsgpu_invert_matrix(rsgpu_ctx *c, const uint8_t *matrix, uint8_t *inverse, i
     if (e == cudaSuccess) e = cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaMemcpyAsync(inverse, d + (size_t)n * n, (size_t)n * n, cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
-    cudaFree(d);
     if (e != cudaSuccess) return fail_cuda(e, "rsgpu_invert_matrix");
     ++c->launches;
     if (flag) return fail_msg(RSGPU_ESINGULAR, "matrix is singular");
@@ -545,6 +608,7 @@ int rsgpu_matmul(rsgpu_ctx *c, const uint8_t *matrix, int rows, const uint8_t *i
 {
     if (!c || !matrix || !in_d || !out_d) return fail_msg(RSGPU_EINVAL, "NULL argument");
     if (rows < 1 || rows > 255) return fail_msg(RSGPU_EINVAL, "need 1 <= rows <= 255");
+    if ((c->k > 1 && in_pitch < len) || (rows > 1 && out_pitch < len)) return fail_msg(RSGPU_EINVAL, "pitch < len");
     int rc = ctx_bind(c);
     if (rc) return rc;
     if (c->scratch.rows != rows || !c->scratch.d_matrix)

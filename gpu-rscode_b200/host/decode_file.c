@@ -103,8 +103,11 @@ void decode_file(char *inFile, char *confFile, char *outFile, int gridDimXSize, 
     }
     /* all k natives land in ONE file: map it so the IO threads store into it in parallel (pwrite on a
      * single inode serialises; measured 3 GB/s on tmpfs).  Fall back to pwrite if the mapping fails. */
+    /* The blocks are reserved first (posix_fallocate): a store into a sparse mapping of a full or
+     * over-quota file system raises SIGBUS, which no error path can catch; if the space cannot be had the
+     * pwrite path reports "fwrite error!" the ordinary way. */
     uint8_t *out_map = NULL;
-    if (md.total_size > 0 && ftruncate(fd_out, (off_t)md.total_size) == 0) {
+    if (md.total_size > 0 && posix_fallocate(fd_out, 0, (off_t)md.total_size) == 0) {
         void *m = mmap(NULL, (size_t)md.total_size, PROT_READ | PROT_WRITE, MAP_SHARED, fd_out, 0);
         if (m != MAP_FAILED)
             out_map = m;
@@ -161,8 +164,12 @@ void decode_file(char *inFile, char *confFile, char *outFile, int gridDimXSize, 
     }
     printf("Total GPU decoding time using multiple devices: %fms\n", wall_ms); /* src/decode.cu:224 */
 
-    if (out_map)
-        munmap(out_map, (size_t)md.total_size);
+    if (out_map && (msync(out_map, (size_t)md.total_size, MS_SYNC) != 0 || munmap(out_map, (size_t)md.total_size) != 0)) {
+        close(fd_out);
+        unlink(tmp_name);
+        printf("fwrite error!\n"); /* a late write-back failure is a failed write, not a success */
+        exit(0);
+    }
     if (ftruncate(fd_out, (off_t)md.total_size) != 0 || close(fd_out) != 0 || rename(tmp_name, out_name) != 0) {
         printf("fwrite error!\n");
         exit(0);

@@ -48,9 +48,19 @@ int rs_read_metadata(const char *path, rs_metadata *md)
     uint8_t *m = malloc(n ? n : 1);
     size_t got = 0;
     int v;
-    while (m && got < n && fscanf(fp, "%d", &v) == 1)
+    int bad = 0;
+    while (m && got < n && fscanf(fp, "%d", &v) == 1) {
+        if (v < 0 || v > 255) { /* not a field element: refuse rather than truncate silently */
+            bad = 1;
+            break;
+        }
         m[got++] = (uint8_t)v;
+    }
     fclose(fp);
+    if (bad) {
+        free(m);
+        return -2;
+    }
     if (m && got == n) {
         md->matrix = m;
     } else {

@@ -55,6 +55,7 @@ struct rs_stream {
     int error;
     char error_text[512];
     double gpu_ms[64];
+    int gpu_slabs[64];   /* slabs each GPU worker coded */
     double t_start;
 };
 
@@ -220,6 +221,7 @@ static void *gpu_main(void *arg)
 
         pthread_mutex_lock(&st->mu);
         st->gpu_ms[ga->gpu] += 1e3 * dt;
+        ++st->gpu_slabs[ga->gpu];
         if (rc != RSGPU_OK) {
             snprintf(text, sizeof text, "GPU %d: coding failed: %s (%s)", ga->gpu, rsgpu_strerror(rc), rsgpu_last_error());
             set_error(st, rc, text);
@@ -376,6 +378,9 @@ int rs_stream_run(const rs_stream_desc *desc, double *wall_ms, int *n_gpus_used,
     if (wall_ms) *wall_ms = 1e3 * (t_pipe - t0);
     if (getenv("RS_TIMING"))
         fprintf(stderr, "[rs timing] pipeline %.1f ms, context teardown %.1f ms\n", 1e3 * (t_pipe - t0), 1e3 * (now_s() - t_pipe));
+    if (getenv("RS_TIMING"))
+        for (int g = 0; g < st.n_gpus; ++g)
+            fprintf(stderr, "[rs timing] GPU %d coded %d of %lld slabs\n", g, st.gpu_slabs[g], st.n_slabs);
     for (int g = 0; g < st.n_gpus; ++g)
         printf("Device%d: Total GPU %s time: %fms\n", g, desc->decode ? "decoding" : "encoding", st.gpu_ms[g]);
 

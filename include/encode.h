@@ -8,9 +8,11 @@
  *                   prints "Valid grid size: (0, %d]" and uses the default, src/encode.cu:348-355)
  *   streamNum       the reference's -s: number of pipeline slots (streams) per GPU
  *
- * Behaviour kept: blocking call, one worker thread per visible GPU each taking a contiguous byte range
- * of every fragment, IO errors print the reference's message and exit(0), the "Total GPU encoding
- * time using multiple devices" line.  Changed on purpose: 64-bit sizes (files >= 2 GiB work), the
+ * Behaviour kept: blocking call, IO errors print the reference's message and exit(0), the "Total GPU
+ * encoding time using multiple devices" line, no exchange between GPUs.  How the work is spread differs from
+ * the reference (one pthread per visible GPU, each a contiguous byte range, src/encode.cu:357-403): the
+ * column space is cut into slabs that go to whichever GPU worker is free, and a job starts one GPU worker
+ * per 32 GiB of input (RS_GPUS=<n> overrides) because every further CUDA context costs start-up time.  Changed on purpose: 64-bit sizes (files >= 2 GiB work), the
  * tail of the last native fragment is zero-padded as in cpu-rs.c:502 (the GPU reference leaves
  * malloc garbage there, src/encode.cu:325), no cudaDeviceReset on return.
  */

@@ -366,6 +366,34 @@ def test_set_survivors_while_previous_decode_is_in_flight(rs, torch):
             assert torch.equal(out, data), f"step {i}"
 
 
+def test_decode_on_several_streams_right_after_set_survivors(rs, torch):
+    """One context, several streams: the tables of the full k x k plan are built on first use, so a decode on a
+    SECOND stream must wait for that build (queued by the first), and rsgpu_set_survivors must wait for the
+    decodes of every stream before it rewrites a table set -- not only for the stream used last.  Six streams
+    (more than the tracker has slots) decode concurrently, survivor sets change without host synchronisation."""
+    k, p, L = 10, 4, 24 << 20
+    s0 = torch.cuda.current_stream().cuda_stream
+    streams = [torch.cuda.Stream() for _ in range(6)]
+    data = torch.randint(0, 256, (k, L), dtype=torch.uint8, device="cuda")
+    orders = [[10, 11, 12, 13, 4, 5, 6, 7, 8, 9], [0, 1, 2, 3, 4, 5, 10, 11, 12, 13], [13, 1, 12, 3, 11, 5, 10, 7, 8, 9]]
+    with rs.RSContext(k, p) as ctx:
+        parity = torch.empty((p, L), dtype=torch.uint8, device="cuda")
+        ctx.encode(data.data_ptr(), L, parity.data_ptr(), L, L, s0)
+        frags = torch.cat([data, parity])
+        survs = [frags[torch.tensor(o, device="cuda")].contiguous() for o in orders]
+        outs = [[torch.zeros((k, L), dtype=torch.uint8, device="cuda") for _ in streams] for _ in range(4)]
+        torch.cuda.synchronize()
+        for rnd, row in enumerate(outs):
+            o = rnd % len(orders)
+            ctx.set_survivors(orders[o])
+            for st, out in zip(streams, row):      # first call builds the tables; the others must wait for them
+                ctx.decode(survs[o].data_ptr(), L, out.data_ptr(), L, L, st.cuda_stream)
+        torch.cuda.synchronize()
+        for rnd, row in enumerate(outs):
+            for i, out in enumerate(row):
+                assert torch.equal(out, data), f"round {rnd}, stream {i}"
+
+
 def test_gpu_encode_then_gpu_decode_all_double_erasures_rs46(rs, torch):
     k, p, L = 4, 2, 3_001
     data = splitmix64_bytes(9, k * L).reshape(k, L)

@@ -24,11 +24,12 @@ def main():
     ap.add_argument("--threads", default="0")
     ap.add_argument("--blocks", default="0")
     ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--extra-bytes", type=int, default=0, help="add this many bytes to the fragment length; pitch = length (unaligned rows)")
     args = ap.parse_args()
     import torch
     rs = importlib.import_module("gpu-rscode_b200")
     k, p = args.k, args.p
-    L = int(args.frag_mib * (1 << 20)) // 256 * 256
+    L = int(args.frag_mib * (1 << 20)) // 256 * 256 + args.extra_bytes
     try:
         peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     except Exception:
