@@ -69,8 +69,9 @@ template <int OFF> __device__ __forceinline__ uint32_t lds32_pinned(uint32_t add
 template <int W> struct Acc;
 // t: bit-7 terms of the fat7 fragments, kept TRANSPOSED (t[4*row + word]: four byte positions of one output
 // row per register, i.e. already in store order) -- see mac_vec
-template <> struct Acc<4> { uint32_t a[16]; uint32_t t[16]; };
-template <> struct Acc<8> { uint32_t a[16]; uint32_t b[16]; };
+// x: the peeled all-ones row (XR instances): plain XOR of the input vectors, already in store order
+template <> struct Acc<4> { uint32_t a[16]; uint32_t t[16]; uint4 x; };
+template <> struct Acc<8> { uint32_t a[16]; uint32_t b[16]; uint4 x; };
 
 // Shared-memory map for a K-fragment code (all offsets relative to the 256-aligned base tb):
 //   fragments [0, N8)        fat8 tables, 32 KiB each
@@ -178,13 +179,41 @@ __device__ __forceinline__ void mac_vec(const uint4 &d, uint32_t lane_base, uint
     mac_word<W, K, J, T7, XB>(d.w, lane_base, tb, c7a, c7b, acc, 12);
 }
 
+// XR: the coding matrix has an all-ones row (row 0 of the reference's Vandermonde generator, (j+1)^0,
+// src/matrix.cu:758) that was peeled off the tables: that output row is the XOR of the inputs, one LOP3 per word
+// instead of a lookup per byte -- which lets five parity rows run on 32-bit table entries (four looked-up rows +
+// the XOR row) instead of 64-bit ones (two shared-memory wavefronts per lookup).
+template <bool XR, int W>
+__device__ __forceinline__ void xor_row_acc(Acc<W> &acc, const uint4 &d)
+{
+    if constexpr (XR) {
+        acc.x.x ^= d.x;
+        acc.x.y ^= d.y;
+        acc.x.z ^= d.z;
+        acc.x.w ^= d.w;
+    }
+}
+
+template <bool XR, bool T7, int W>
+__device__ __forceinline__ void acc_clear(Acc<W> &acc)
+{
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        acc.a[i] = 0;
+        if constexpr (W == 8) acc.b[i] = 0;
+        else if constexpr (T7) acc.t[i] = 0;
+    }
+    if constexpr (XR) acc.x = make_uint4(0u, 0u, 0u, 0u);
+}
+
 // compile-time loop over the fragments of batch B
-template <int W, int K, int JB, int B, int JJ, bool T7, int XB = 0>
+template <int W, int K, int JB, int B, int JJ, bool T7, int XB = 0, bool XR = false>
 struct BatchMac {
     __device__ __forceinline__ static void run(const uint4 (&d)[JB], uint32_t lane_base, uint32_t tb, Acc<W> &acc)
     {
         mac_vec<W, K, B * JB + JJ, T7, XB>(d[JJ], lane_base, tb, acc);
-        if constexpr (JJ + 1 < JB) BatchMac<W, K, JB, B, JJ + 1, T7, XB>::run(d, lane_base, tb, acc);
+        xor_row_acc<XR>(acc, d[JJ]);
+        if constexpr (JJ + 1 < JB) BatchMac<W, K, JB, B, JJ + 1, T7, XB, XR>::run(d, lane_base, tb, acc);
     }
 };
 

@@ -45,7 +45,7 @@ __device__ __forceinline__ size_t out_off(const Pos &p, const BatchGeom &g) { re
 
 // As ColumnBatches of gf_matmul_fat_sm100.cu, with the next column given as a pointer (nullptr = none) and the
 // prefetch distances as 64-bit byte deltas (the next column may sit in another stripe).
-template <int W, int K, int JB, int KB, int B, int SP, bool PF, bool T7, bool PAD>
+template <int W, int K, int JB, int KB, int B, int SP, bool PF, bool T7, bool PAD, bool XR>
 struct ColumnBatchesB {
     __device__ __forceinline__ static void run(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
                                                const uint8_t *q_next, uint32_t lane_base, uint32_t tb, Acc<W> &acc,
@@ -62,13 +62,13 @@ struct ColumnBatchesB {
                 load_batch<JB, PF, PAD, 0>(nxt, q, in_pitch, pf1, k);
             }
         }
-        BatchMac<W, K, JB, B, 0, T7>::run(cur, lane_base, tb, acc);
+        BatchMac<W, K, JB, B, 0, T7, 0, XR>::run(cur, lane_base, tb, acc);
         if constexpr (B + 1 < KB)
-            ColumnBatchesB<W, K, JB, KB, B + 1, SP, PF, T7, PAD>::run(buf0, buf1, q, in_pitch, q_next, lane_base, tb, acc, pf0, pf1, k);
+            ColumnBatchesB<W, K, JB, KB, B + 1, SP, PF, T7, PAD, XR>::run(buf0, buf1, q, in_pitch, q_next, lane_base, tb, acc, pf0, pf1, k);
     }
 };
 
-template <int W, int K, int JB, int KB, int SP, bool PF, bool T7, bool PAD>
+template <int W, int K, int JB, int KB, int SP, bool PF, bool T7, bool PAD, bool XR>
 __device__ __forceinline__ void do_column_b(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
                                             const uint8_t *in, uint8_t *out, size_t out_pitch, const Pos &p, const Pos &pn,
                                             const Pos &pnn, const BatchGeom &g, uint32_t lane_base, uint32_t tb, int nrows, int k)
@@ -80,13 +80,8 @@ __device__ __forceinline__ void do_column_b(uint4 (&buf0)[JB], uint4 (&buf1)[JB]
     const ptrdiff_t pf0 = has_n ? (ptrdiff_t)(on - o) : 0;
     const ptrdiff_t pf1 = has_nn ? (ptrdiff_t)(in_off(pnn, g) - on) : 0;
     Acc<W> acc;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        acc.a[i] = 0;
-        if constexpr (W == 8) acc.b[i] = 0;
-        else if constexpr (T7) acc.t[i] = 0;
-    }
-    ColumnBatchesB<W, K, JB, KB, 0, SP, PF, T7, PAD>::run(buf0, buf1, q, in_pitch, has_n ? in + on : nullptr, lane_base, tb, acc, pf0, pf1, k);
+    acc_clear<XR, T7>(acc);
+    ColumnBatchesB<W, K, JB, KB, 0, SP, PF, T7, PAD, XR>::run(buf0, buf1, q, in_pitch, has_n ? in + on : nullptr, lane_base, tb, acc, pf0, pf1, k);
     const size_t oo = out_off(p, g);
     if constexpr (W == 8) {
         transpose_store(acc.a, out, out_pitch, oo, 0, nrows);
@@ -94,9 +89,10 @@ __device__ __forceinline__ void do_column_b(uint4 (&buf0)[JB], uint4 (&buf1)[JB]
     } else {
         transpose_store(acc.a, out, out_pitch, oo, 0, nrows, (T7 && Map<K>::NF > Map<K>::N8) ? acc.t : nullptr);
     }
+    if constexpr (XR) stg_stream(out - out_pitch + oo, acc.x);   // the peeled all-ones row, right above the group's rows
 }
 
-template <int W, int JB, int KB, bool PF, bool T7, bool PAD>
+template <int W, int JB, int KB, bool PF, bool T7, bool PAD, bool XR>
 __global__ void __launch_bounds__(fat_threads(W, JB, T7), 1)
 k_gf_matmul_fat_batch(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
                       const uint32_t *__restrict__ tab, int nrows, BatchGeom g, int k)
@@ -121,13 +117,13 @@ k_gf_matmul_fat_batch(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *
         load_batch<JB, PF, PAD, 0>(buf0, q, in_pitch, valid(pn, g) ? (ptrdiff_t)(in_off(pn, g) - in_off(p, g)) : (ptrdiff_t)0, k);
 
     while (valid(p, g)) {
-        do_column_b<W, K, JB, KB, 0, PF, T7, PAD>(buf0, buf1, q, in_pitch, in, out, out_pitch, p, pn, pnn, g, lane_base, tb, nrows, k);
+        do_column_b<W, K, JB, KB, 0, PF, T7, PAD, XR>(buf0, buf1, q, in_pitch, in, out, out_pitch, p, pn, pnn, g, lane_base, tb, nrows, k);
         p = pn;
         pn = pnn;
         advance(pnn, g);
         if constexpr (KB & 1) {          // odd batch count: the next column starts in the other buffer
             if (!valid(p, g)) break;
-            do_column_b<W, K, JB, KB, 1, PF, T7, PAD>(buf0, buf1, q, in_pitch, in, out, out_pitch, p, pn, pnn, g, lane_base, tb, nrows, k);
+            do_column_b<W, K, JB, KB, 1, PF, T7, PAD, XR>(buf0, buf1, q, in_pitch, in, out, out_pitch, p, pn, pnn, g, lane_base, tb, nrows, k);
             p = pn;
             pn = pnn;
             advance(pnn, g);
@@ -143,20 +139,20 @@ struct FatBatchKernel {
     int smem;
 };
 
-template <int W, int JB, int KB, bool PAD>
+template <int W, int JB, int KB, bool PAD, bool XR>
 FatBatchKernel make_fat_batch()
 {
     constexpr int K = JB * KB;
     constexpr bool PF = fat_use_prefetch(K), T7 = fat_use_t7(W, K);
-    return FatBatchKernel{k_gf_matmul_fat_batch<W, JB, KB, PF, T7, PAD>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
+    return FatBatchKernel{k_gf_matmul_fat_batch<W, JB, KB, PF, T7, PAD, XR>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
 }
 
 // the same shape per k as the single-stripe kernel (RSGPU_FAT_SHAPES, gf_matmul_fat.cuh)
-template <int W>
+template <int W, bool XR = false>
 bool pick_fat_batch(int k, FatBatchKernel *fk)
 {
     switch (k) {
-#define RSGPU_FAT_CASE(k_, jb_, kb_, pad_) case k_: *fk = make_fat_batch<W, jb_, kb_, pad_>(); return true;
+#define RSGPU_FAT_CASE(k_, jb_, kb_, pad_) case k_: *fk = make_fat_batch<W, jb_, kb_, pad_, XR>(); return true;
         RSGPU_FAT_SHAPES(RSGPU_FAT_CASE)
 #undef RSGPU_FAT_CASE
     default: return false;
@@ -173,7 +169,9 @@ cudaError_t launch_matmul_fat_batch(const RowGroup &g, int k, const uint8_t *in,
                                     const DeviceInfo &dev, int max_blocks, cudaStream_t s)
 {
     FatBatchKernel fk;
-    const bool ok = g.width == 4 ? pick_fat_batch<4>(k, &fk) : pick_fat_batch<8>(k, &fk);
+    if (g.xor_row >= 0 && g.width != 4) return cudaErrorNotSupported;
+    const bool ok = g.xor_row >= 0 ? pick_fat_batch<4, true>(k, &fk)
+                                   : (g.width == 4 ? pick_fat_batch<4>(k, &fk) : pick_fat_batch<8>(k, &fk));
     if (!ok || fk.smem > dev.max_smem_optin) return cudaErrorNotSupported;
     if (nvec == 0 || nvec >= ((size_t)1 << 31) || n_stripes == 0 || n_stripes >= ((size_t)1 << 31)) return cudaErrorNotSupported;
     int occ = 0;

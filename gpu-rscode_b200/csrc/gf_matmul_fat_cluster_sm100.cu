@@ -218,7 +218,7 @@ ClusterKernel make_cluster()
 cudaError_t launch_matmul_fat_cluster(const RowGroup &g, int k, const uint8_t *in, size_t in_pitch, uint8_t *out_g,
                                       size_t out_pitch, size_t nvec, const DeviceInfo &dev, int max_blocks, cudaStream_t s)
 {
-    if (g.width != 4 || k < 17 || k > 32) return cudaErrorNotSupported;
+    if (g.width != 4 || k < 17 || k > 32 || g.xor_row >= 0) return cudaErrorNotSupported;
     // half of k, rounded up to a shape with an even batch count
     ClusterKernel ck = k <= 20 ? make_cluster<5, 2>() : (k <= 24 ? make_cluster<3, 4>() : (k <= 28 ? make_cluster<7, 2>() : make_cluster<4, 4>()));
     if (ck.smem > dev.max_smem_optin) return cudaErrorNotSupported;

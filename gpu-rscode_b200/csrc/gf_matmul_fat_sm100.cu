@@ -29,7 +29,7 @@ namespace {
 // buffers alternate per batch ("ping-pong"): the loads of batch t+1 go into the buffer batch t-1 has just
 // released and are issued BEFORE batch t is consumed, so they have a whole batch of work to land and no
 // register-to-register copies are needed.  SP = which buffer holds batch 0 of this column.
-template <int W, int K, int JB, int KB, int B, int SP, bool PF, bool T7, bool PAD>
+template <int W, int K, int JB, int KB, int B, int SP, bool PF, bool T7, bool PAD, bool XR>
 struct ColumnBatches {
     __device__ __forceinline__ static void run(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
                                                const uint8_t *in, size_t vn, size_t nvec, uint32_t lane_base,
@@ -46,13 +46,13 @@ struct ColumnBatches {
                 load_batch<JB, PF, PAD, 0>(nxt, q, in_pitch, pf1, k);
             }
         }
-        BatchMac<W, K, JB, B, 0, T7>::run(cur, lane_base, tb, acc);
+        BatchMac<W, K, JB, B, 0, T7, 0, XR>::run(cur, lane_base, tb, acc);
         if constexpr (B + 1 < KB)
-            ColumnBatches<W, K, JB, KB, B + 1, SP, PF, T7, PAD>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1, k);
+            ColumnBatches<W, K, JB, KB, B + 1, SP, PF, T7, PAD, XR>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1, k);
     }
 };
 
-template <int W, int K, int JB, int KB, int SP, bool PF, bool T7, bool PAD>
+template <int W, int K, int JB, int KB, int SP, bool PF, bool T7, bool PAD, bool XR>
 __device__ __forceinline__ void do_column(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, size_t in_pitch,
                                           const uint8_t *in, uint8_t *out, size_t out_pitch, size_t v, size_t vn,
                                           size_t nvec, uint32_t lane_base, uint32_t tb, int nrows, uint32_t pf_stride,
@@ -62,22 +62,18 @@ __device__ __forceinline__ void do_column(uint4 (&buf0)[JB], uint4 (&buf1)[JB], 
     const uint32_t pf0 = vn < nvec ? pf_stride : 0u;
     const uint32_t pf1 = vn + (vn - v) < nvec ? pf_stride : 0u;
     Acc<W> acc;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        acc.a[i] = 0;
-        if constexpr (W == 8) acc.b[i] = 0;
-        else if constexpr (T7) acc.t[i] = 0;
-    }
-    ColumnBatches<W, K, JB, KB, 0, SP, PF, T7, PAD>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1, k);
+    acc_clear<XR, T7>(acc);
+    ColumnBatches<W, K, JB, KB, 0, SP, PF, T7, PAD, XR>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1, k);
     if constexpr (W == 8) {
         transpose_store(acc.a, out, out_pitch, v * 16, 0, nrows);
         transpose_store(acc.b, out, out_pitch, v * 16, 4, nrows - 4);
     } else {
         transpose_store(acc.a, out, out_pitch, v * 16, 0, nrows, (T7 && Map<K>::NF > Map<K>::N8) ? acc.t : nullptr);
     }
+    if constexpr (XR) stg_stream(out - out_pitch + v * 16, acc.x);   // the peeled row sits right above the group's rows
 }
 
-template <int W, int JB, int KB, bool PF, bool T7, bool PAD>
+template <int W, int JB, int KB, bool PF, bool T7, bool PAD, bool XR>
 __global__ void __launch_bounds__(fat_threads(W, JB, T7), 1)
 k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
                 const uint32_t *__restrict__ tab, int nrows, size_t nvec, int k)
@@ -99,11 +95,11 @@ k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__rest
     if (v < nvec) load_batch<JB, PF, PAD, 0>(buf0, q, in_pitch, v + stride < nvec ? pf_stride : 0u, k);
 
     while (v < nvec) {
-        do_column<W, K, JB, KB, 0, PF, T7, PAD>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride, k);
+        do_column<W, K, JB, KB, 0, PF, T7, PAD, XR>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride, k);
         v += stride;
         if constexpr (KB & 1) {          // odd batch count: the next column starts in the other buffer
             if (v >= nvec) break;
-            do_column<W, K, JB, KB, 1, PF, T7, PAD>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride, k);
+            do_column<W, K, JB, KB, 1, PF, T7, PAD, XR>(buf0, buf1, q, in_pitch, in, out, out_pitch, v, v + stride, nvec, lane_base, tb, nrows, pf_stride, k);
             v += stride;
         }
     }
@@ -117,7 +113,7 @@ struct FatKernel {
     int smem;
 };
 
-template <int W, int JB, int KB, bool PAD = false>
+template <int W, int JB, int KB, bool PAD = false, bool XR = false>
 FatKernel make_fat()
 {
     // L2 prefetch one stride ahead: on from k = 8.  Same box, same build, off -> on (fraction of the measured
@@ -130,14 +126,14 @@ FatKernel make_fat()
     // (RS(10,14) 0.930 -> 0.754, RS(12,16) 0.878 -> 0.639).
     constexpr int K = JB * KB;
     constexpr bool T7 = fat_use_t7(W, K);
-    return FatKernel{k_gf_matmul_fat<W, JB, KB, PF, T7, PAD>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
+    return FatKernel{k_gf_matmul_fat<W, JB, KB, PF, T7, PAD, XR>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
 }
 
-template <int W>
+template <int W, bool XR = false>
 bool pick_fat(int k, FatKernel *fk)
 {
     switch (k) {
-#define RSGPU_FAT_CASE(k_, jb_, kb_, pad_) case k_: *fk = make_fat<W, jb_, kb_, pad_>(); return true;
+#define RSGPU_FAT_CASE(k_, jb_, kb_, pad_) case k_: *fk = make_fat<W, jb_, kb_, pad_, XR>(); return true;
         RSGPU_FAT_SHAPES(RSGPU_FAT_CASE)
 #undef RSGPU_FAT_CASE
     default: return false;
@@ -153,7 +149,8 @@ cudaError_t launch_matmul_fat(const RowGroup &g, int k, const uint8_t *in, size_
                               cudaStream_t s)
 {
     FatKernel fk;
-    const bool ok = g.width == 4 ? pick_fat<4>(k, &fk) : pick_fat<8>(k, &fk);
+    if (g.xor_row >= 0 && g.width != 4) return cudaErrorNotSupported;     // the peeled row exists with 32-bit entries only
+    const bool ok = g.xor_row >= 0 ? pick_fat<4, true>(k, &fk) : (g.width == 4 ? pick_fat<4>(k, &fk) : pick_fat<8>(k, &fk));
     if (!ok || fk.smem > dev.max_smem_optin) return cudaErrorNotSupported;
     if (threads > 0 && threads < fk.threads) fk.threads = threads;   // tuning: fewer threads than the launch bound
     int occ = 0;   // always 1: the tables fill the SM's shared memory; the call raises the opt-in attribute once

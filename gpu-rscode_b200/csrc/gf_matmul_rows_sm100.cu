@@ -16,6 +16,7 @@ namespace {
 
 struct OutRows {
     uint8_t *r[8];
+    uint8_t *x;      // destination of the peeled all-ones row (plain XOR of the inputs), or nullptr
 };
 
 __device__ __forceinline__ void transpose_store_rows(const uint32_t *a, const OutRows &rows, size_t off, int row0, int nrows)
@@ -62,6 +63,7 @@ k_gf_matmul_rows(const uint8_t *__restrict__ in, size_t in_pitch, OutRows rows, 
     while (v < nvec) {
         Acc<W> acc;
         acc_clear<W>(acc);
+        uint4 x = make_uint4(0u, 0u, 0u, 0u);
         const size_t vn = v + stride;
         for (int b = 0; b < kb; ++b) {
             uint4 cur[JB];
@@ -76,10 +78,19 @@ k_gf_matmul_rows(const uint8_t *__restrict__ in, size_t in_pitch, OutRows rows, 
             }
             const uint32_t t0 = tb + (uint32_t)(b * JB) * 256u;
 #pragma unroll
-            for (int jj = 0; jj < JB; ++jj) mac_vec<W, 2>(cur[jj], t0 + jj * 256u, hi4, acc);
+            for (int jj = 0; jj < JB; ++jj) {
+                mac_vec<W, 2>(cur[jj], t0 + jj * 256u, hi4, acc);
+                if (rows.x && (!PAD || b * JB + jj < k)) {   // uniform: this kernel is NVLink-bound, a runtime test is free
+                    x.x ^= cur[jj].x;
+                    x.y ^= cur[jj].y;
+                    x.z ^= cur[jj].z;
+                    x.w ^= cur[jj].w;
+                }
+            }
         }
         transpose_store_rows(acc.a, rows, v * 16, 0, nrows);
         if constexpr (W == 8) transpose_store_rows(acc.b, rows, v * 16, 4, nrows - 4);
+        if (rows.x) stg_stream(rows.x + v * 16, x);
         v = vn;
     }
 }
@@ -92,8 +103,10 @@ k_gf_matmul_rows_bytes(const uint8_t *__restrict__ in, size_t in_pitch, OutRows 
 {
     for (size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; c < len; c += (size_t)gridDim.x * blockDim.x) {
         uint32_t a = 0, b = 0;
+        unsigned xs = 0;
         for (int j = 0; j < k; ++j) {
             const unsigned x = in[(size_t)j * in_pitch + c];
+            xs ^= x;
             const uint32_t *tl = tab + (size_t)j * 32 * (W / 4), *th = tl + 16 * (W / 4);
             if (W == 4) {
                 a ^= __ldg(tl + (x & 15u)) ^ __ldg(th + (x >> 4));
@@ -103,6 +116,7 @@ k_gf_matmul_rows_bytes(const uint8_t *__restrict__ in, size_t in_pitch, OutRows 
             }
         }
         for (int r = 0; r < nrows; ++r) rows.r[r][c] = (uint8_t)((r < 4 ? a : b) >> (8 * (r & 3)));
+        if (rows.x) rows.x[c] = (uint8_t)xs;
     }
 }
 
@@ -120,6 +134,8 @@ cudaError_t launch_matmul_rows(const RowGroup &g, int k, int kpad, const uint8_t
         rows.r[i] = i < g.nrows ? out_rows[g.row0 + i] : nullptr;
         if (i < g.nrows && ((uintptr_t)rows.r[i] & 15u)) aligned = false;
     }
+    rows.x = g.xor_row >= 0 ? out_rows[g.xor_row] : nullptr;
+    if ((uintptr_t)rows.x & 15u) aligned = false;
     const size_t nvec = aligned ? len / 16 : 0;
     const uint32_t hi4 = 16u * g.width * 0x01010101u;
     if (nvec) {

@@ -29,7 +29,7 @@ namespace {
 
 // W: table entry bytes (4: up to 4 output rows, 8: up to 8).  JB: fragments per load batch.
 // kb = number of batches (kb*JB >= k, kb*JB <= kpad); PAD = (kb*JB > k).
-template <int W, int JB, int EX, bool PAD>
+template <int W, int JB, int EX, bool PAD, bool XR = false>
 __global__ void __launch_bounds__(256)
 k_gf_matmul(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
             const uint32_t *__restrict__ tab, int npages, int k, int kb, int nrows, size_t nvec, uint32_t hi4)
@@ -59,6 +59,7 @@ k_gf_matmul(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict
     while (v < nvec) {
         Acc<W> acc;
         acc_clear<W>(acc);
+        uint4 x = make_uint4(0u, 0u, 0u, 0u);     // XR: the peeled all-ones row (see gf_matmul_fat.cuh)
         const size_t vn = v + stride;
         for (int b = 0; b < kb; ++b) {
             uint4 cur[JB];
@@ -73,10 +74,22 @@ k_gf_matmul(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict
             }
             const uint32_t t0 = tb + (uint32_t)(b * JB) * 256u;
 #pragma unroll
-            for (int jj = 0; jj < JB; ++jj) mac_vec<W, EX>(cur[jj], t0 + jj * 256u, hi4, acc);
+            for (int jj = 0; jj < JB; ++jj) {
+                mac_vec<W, EX>(cur[jj], t0 + jj * 256u, hi4, acc);
+                if constexpr (XR) {
+                    // padded slots re-read the last valid row: they must not enter the XOR twice
+                    if (!PAD || b * JB + jj < k) {
+                        x.x ^= cur[jj].x;
+                        x.y ^= cur[jj].y;
+                        x.z ^= cur[jj].z;
+                        x.w ^= cur[jj].w;
+                    }
+                }
+            }
         }
         transpose_store(acc.a, out, out_pitch, v * 16, 0, nrows);
         if constexpr (W == 8) transpose_store(acc.b, out, out_pitch, v * 16, 4, nrows - 4);
+        if constexpr (XR) stg_stream(out - out_pitch + v * 16, x);
         v = vn;
     }
 }
@@ -86,13 +99,15 @@ k_gf_matmul(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict
 template <int W>
 __global__ void __launch_bounds__(256)
 k_gf_matmul_bytes(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
-                  const uint32_t *__restrict__ tab, int k, int nrows, size_t c0, size_t len)
+                  const uint32_t *__restrict__ tab, int k, int nrows, size_t c0, size_t len, int xr)
 {
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; c < len; c += stride) {
         uint32_t a = 0, b = 0;
+        unsigned xs = 0;       // xr: the peeled all-ones row, written one row above the group's rows
         for (int j = 0; j < k; ++j) {
             const unsigned x = in[(size_t)j * in_pitch + c];
+            xs ^= x;
             const uint32_t *tl = tab + (size_t)j * 32 * (W / 4);
             const uint32_t *th = tl + 16 * (W / 4);
             if (W == 4) {
@@ -106,6 +121,7 @@ k_gf_matmul_bytes(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__re
             const uint32_t wv = r < 4 ? a : b;
             out[(size_t)r * out_pitch + c] = (uint8_t)(wv >> (8 * (r & 3)));
         }
+        if (xr) (out - out_pitch)[c] = (uint8_t)xs;
     }
 }
 
@@ -114,15 +130,17 @@ template <int W>
 __global__ void __launch_bounds__(256)
 k_gf_matmul_bytes_batch(const uint8_t *__restrict__ in, size_t in_pitch, size_t in_stripe, uint8_t *__restrict__ out,
                         size_t out_pitch, size_t out_stripe, const uint32_t *__restrict__ tab, int k, int nrows, size_t c0,
-                        unsigned rem, size_t n_stripes)
+                        unsigned rem, size_t n_stripes, int xr)
 {
     const size_t total = n_stripes * rem, stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
         const size_t st = i / rem, c = c0 + (i - st * rem);
         const uint8_t *src = in + st * in_stripe + c;
         uint32_t a = 0, b = 0;
+        unsigned xs = 0;
         for (int j = 0; j < k; ++j) {
             const unsigned x = src[(size_t)j * in_pitch];
+            xs ^= x;
             const uint32_t *tl = tab + (size_t)j * 32 * (W / 4);
             const uint32_t *th = tl + 16 * (W / 4);
             if (W == 4) {
@@ -137,6 +155,7 @@ k_gf_matmul_bytes_batch(const uint8_t *__restrict__ in, size_t in_pitch, size_t 
             const uint32_t wv = r < 4 ? a : b;
             dst[(size_t)r * out_pitch] = (uint8_t)(wv >> (8 * (r & 3)));
         }
+        if (xr) *(dst - out_pitch) = (uint8_t)xs;
     }
 }
 
@@ -154,6 +173,21 @@ MatmulFn pick_jb(int jb, bool pad)
     case 6: return pad ? k_gf_matmul<W, 6, EX, true> : k_gf_matmul<W, 6, EX, false>;
     case 7: return pad ? k_gf_matmul<W, 7, EX, true> : k_gf_matmul<W, 7, EX, false>;
     default: return pad ? k_gf_matmul<W, 8, EX, true> : k_gf_matmul<W, 8, EX, false>;
+    }
+}
+
+// the peeled-row instances: 32-bit entries, DP4A extraction only
+MatmulFn pick_kernel_xr(int jb, bool pad)
+{
+    switch (jb) {
+    case 1: return k_gf_matmul<4, 1, 2, false, true>;
+    case 2: return k_gf_matmul<4, 2, 2, false, true>;
+    case 3: return k_gf_matmul<4, 3, 2, false, true>;
+    case 4: return pad ? k_gf_matmul<4, 4, 2, true, true> : k_gf_matmul<4, 4, 2, false, true>;
+    case 5: return pad ? k_gf_matmul<4, 5, 2, true, true> : k_gf_matmul<4, 5, 2, false, true>;
+    case 6: return pad ? k_gf_matmul<4, 6, 2, true, true> : k_gf_matmul<4, 6, 2, false, true>;
+    case 7: return pad ? k_gf_matmul<4, 7, 2, true, true> : k_gf_matmul<4, 7, 2, false, true>;
+    default: return pad ? k_gf_matmul<4, 8, 2, true, true> : k_gf_matmul<4, 8, 2, false, true>;
     }
 }
 
@@ -222,6 +256,38 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
     const bool aligned = (((uintptr_t)in | (uintptr_t)out_g | in_pitch | out_pitch) & 15u) == 0;
     const size_t nvec = aligned ? len / 16 : 0;
     const int threads = (tune.threads > 0 && tune.threads <= 256) ? tune.threads : 256;
+    const int xr = g.xor_row >= 0;    // this launch also writes the peeled all-ones row, one row above out_g
+    if (xr && (g.width != 4 || g.xor_row != g.row0 - 1)) return cudaErrorInvalidValue;
+
+    // byte-granular kernel over the columns [c0, end)
+    auto launch_bytes = [&](size_t c0, size_t end) -> cudaError_t {
+        if (c0 >= end) return cudaSuccess;
+        size_t blocks = (end - c0 + 255) / 256;
+        const size_t cap = (size_t)dev.sm_count * 8;
+        if (blocks > cap) blocks = cap;
+        if (g.width == 4)
+            k_gf_matmul_bytes<4><<<(unsigned)blocks, 256, 0, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, k, g.nrows, c0, end, xr);
+        else
+            k_gf_matmul_bytes<8><<<(unsigned)blocks, 256, 0, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, k, g.nrows, c0, end, xr);
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess && launches) ++*launches;
+        return e;
+    };
+
+    // Rows that are not 16-byte aligned (a base or a pitch that is not a multiple of 16 -- e.g. pitch = ceil(size/k),
+    // the layout of a file's fragments held back to back): the byte-table kernel with in-register realignment
+    // (gf_matmul_fat_ua_sm100.cu) from 1 MiB per fragment on; its head and tail, shorter stripes and k without an
+    // instance stay on the byte kernel.  Variant 6 forbids it (the byte kernel alone, for comparison).
+    if (!aligned && tune.variant != 6 && len >= ((size_t)1 << 20)) {
+        size_t lo = 0, hi = 0;
+        cudaError_t e = launch_matmul_fat_ua(g, k, in, in_pitch, out_g, out_pitch, len, dev, tune.max_blocks, s, &lo, &hi);
+        if (e == cudaSuccess) {
+            if (launches) ++*launches;
+            if ((e = launch_bytes(0, lo)) != cudaSuccess) return e;
+            return launch_bytes(hi, len);
+        }
+        if (e != cudaErrorNotSupported) return e;
+    }
 
     // variant 0 (default): the bank-replicated kernel when an instance exists for this k and the stripe
     // is long enough to pay for building its tables (one 227 KiB fill per SM: measured break-even
@@ -231,7 +297,7 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
     // through distributed shared memory).  Measured SLOWER than the single-CTA kernel on every such code
     // (RS(24,28) 0.73 vs 0.81, RS(20,24) 0.67 vs 0.87, RS(32,36) 0.66 vs 0.71 of the HBM peak), so it is never
     // chosen automatically; it stays as a tested, selectable experiment (DESIGN.md section 4.1 e)
-    if (nvec && tune.variant == 8) {
+    if (nvec && tune.variant == 8 && !xr) {
         cudaError_t e = launch_matmul_fat_cluster(g, k, in, in_pitch, out_g, out_pitch, nvec, dev, tune.max_blocks, s);
         if (e == cudaSuccess) {
             done_vec = true;
@@ -251,7 +317,7 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
     }
     // next choice: the nibble kernel fed by TMA bulk copies (2-3 % faster than the register-fed one from
     // ~2 MiB per fragment on: RS(16,20) 0.750 vs 0.731, RS(8,12) 0.860 vs 0.838 of the peak); needs k % 8, 5 or 4 == 0
-    if (nvec && !done_vec && (tune.variant == 7 || (tune.variant == 0 && len >= ((size_t)2 << 20)))) {
+    if (nvec && !done_vec && !xr && (tune.variant == 7 || (tune.variant == 0 && len >= ((size_t)2 << 20)))) {
         cudaError_t e = launch_matmul_tma(g, k, kpad, in, in_pitch, out_g, out_pitch, nvec, dev, tune.max_blocks, s);
         if (e == cudaSuccess) {
             done_vec = true;
@@ -266,7 +332,7 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
         if (kb * jb > kpad) return cudaErrorInvalidValue;
         // index extraction: DP4A (default; same speed as the PRMT splice on B200 but the alu pipe sits at
         // 45 % instead of 81 %, profiles/r1_pipes_variant*.csv); variant 1 selects the PRMT splice
-        MatmulFn fn = pick_kernel(g.width, jb, tune.variant == 1, kb * jb > k);
+        MatmulFn fn = xr ? pick_kernel_xr(jb, kb * jb > k) : pick_kernel(g.width, jb, tune.variant == 1, kb * jb > k);
         const size_t smem = (size_t)kpad * 256 + 256;   // one page per fragment + alignment slack
         int occ = 0;
         cudaError_t e = prepare_launch(dev, (const void *)fn, threads, smem, &occ);
@@ -281,19 +347,9 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;
     }
-    const size_t c0 = nvec * 16;
-    if (c0 < len) {
-        const size_t rem = len - c0;
-        size_t blocks = (rem + 255) / 256;
-        const size_t cap = (size_t)dev.sm_count * 8;
-        if (blocks > cap) blocks = cap;
-        if (g.width == 4)
-            k_gf_matmul_bytes<4><<<(unsigned)blocks, 256, 0, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, k, g.nrows, c0, len);
-        else
-            k_gf_matmul_bytes<8><<<(unsigned)blocks, 256, 0, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, k, g.nrows, c0, len);
-        cudaError_t e = cudaGetLastError();
+    if (nvec * 16 < len) {
+        cudaError_t e = launch_bytes(nvec * 16, len);
         if (e != cudaSuccess) return e;
-        if (launches) ++*launches;
     }
     return cudaSuccess;
 }
@@ -309,10 +365,10 @@ cudaError_t launch_matmul_bytes_batch(const RowGroup &g, int k, const uint8_t *i
     if (blocks > cap) blocks = cap;
     if (g.width == 4)
         k_gf_matmul_bytes_batch<4><<<(unsigned)blocks, 256, 0, s>>>(in, in_pitch, in_stripe, out_g, out_pitch, out_stripe, g.d_tab, k,
-                                                                    g.nrows, c0, rem, n_stripes);
+                                                                    g.nrows, c0, rem, n_stripes, g.xor_row >= 0);
     else
         k_gf_matmul_bytes_batch<8><<<(unsigned)blocks, 256, 0, s>>>(in, in_pitch, in_stripe, out_g, out_pitch, out_stripe, g.d_tab, k,
-                                                                    g.nrows, c0, rem, n_stripes);
+                                                                    g.nrows, c0, rem, n_stripes, g.xor_row >= 0);
     return cudaGetLastError();
 }
 

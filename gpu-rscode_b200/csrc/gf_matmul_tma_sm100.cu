@@ -170,7 +170,7 @@ cudaError_t launch_matmul_tma(const RowGroup &g, int k, int kpad, const uint8_t 
             break;
         }
     TmaFn fn = jb ? (g.width == 4 ? pick_tma<4>(jb) : pick_tma<8>(jb)) : nullptr;
-    if (!fn) return cudaErrorNotSupported;
+    if (!fn || g.xor_row >= 0) return cudaErrorNotSupported;    // no peeled-row instances here: the register-fed kernel has them
     const int nst = jb == 8 ? 3 : 4;
     const size_t smem = 256 + (size_t)kpad * 256 + (size_t)nst * jb * kTileBytes + 2 * nst * 8;
     if ((int)smem > dev.max_smem_optin) return cudaErrorNotSupported;

@@ -8,6 +8,8 @@
 // kernel, one strided 2-D copy out, all asynchronous on the slot's stream, and the only host wait is
 // at the very end.  Slices on different slots overlap: H2D of slice i+1, the kernel of slice i and
 // D2H of slice i-1 run on the two copy engines and the SMs at the same time.
+#include <stdlib.h>
+
 #include "../../include/rsgpu.h"
 #include "rs_ctx.h"
 
@@ -65,7 +67,9 @@ static int pipeline_ensure(rsgpu_ctx *c, int slots, size_t pitch, int in_rows, i
 // ring fills quickly and the tail (last kernel + last D2H, not overlapped) stays short.
 static size_t choose_slice(size_t len, int slots)
 {
-    const size_t min_slice = (size_t)1 << 20, max_slice = (size_t)8 << 20;
+    size_t min_slice = (size_t)1 << 20, max_slice = (size_t)8 << 20;
+    if (const char *e = getenv("RSGPU_PIPE_SLICE_MIB"))      // measurement knob: fixed slice length per row
+        if (atoi(e) > 0) min_slice = max_slice = (size_t)atoi(e) << 20;
     size_t s = len / ((size_t)slots * 4);
     if (s < min_slice) s = min_slice;
     if (s > max_slice) s = max_slice;
@@ -83,17 +87,30 @@ static int pipeline_run(rsgpu_ctx *c, const Plan &pl, const uint8_t *in, size_t 
     int rc = pipeline_ensure(c, slots, slice, pl.k, pl.rows);
     if (rc) return rc;
     const size_t pitch = c->slot_pitch;
+    // measurement knob: one contiguous copy per fragment row instead of one strided 2-D copy per slice
+    static const bool row_copies = getenv("RSGPU_PIPE_ROWCOPY") && atoi(getenv("RSGPU_PIPE_ROWCOPY")) > 0;
     int slot = 0;
     for (size_t off = 0; off < len && rc == RSGPU_OK; off += slice, slot = (slot + 1) % slots) {
         const size_t cur = len - off < slice ? len - off : slice;
         cudaStream_t s = c->slot_stream[slot];
-        cudaError_t e = cudaMemcpy2DAsync(c->slot_in[slot], pitch, in + off, in_pitch, cur, pl.k, cudaMemcpyHostToDevice, s);
+        cudaError_t e = cudaSuccess;
+        if (row_copies) {
+            for (int j = 0; j < pl.k && e == cudaSuccess; ++j)
+                e = cudaMemcpyAsync(c->slot_in[slot] + (size_t)j * pitch, in + (size_t)j * in_pitch + off, cur, cudaMemcpyHostToDevice, s);
+        } else {
+            e = cudaMemcpy2DAsync(c->slot_in[slot], pitch, in + off, in_pitch, cur, pl.k, cudaMemcpyHostToDevice, s);
+        }
         if (e != cudaSuccess) {
             rc = fail_cuda(e, "host-to-device slice copy");
             break;
         }
         if ((rc = plan_apply(c, pl, c->slot_in[slot], pitch, c->slot_out[slot], pitch, cur, s)) != RSGPU_OK) break;
-        e = cudaMemcpy2DAsync(out + off, out_pitch, c->slot_out[slot], pitch, cur, pl.rows, cudaMemcpyDeviceToHost, s);
+        if (row_copies) {
+            for (int i = 0; i < pl.rows && e == cudaSuccess; ++i)
+                e = cudaMemcpyAsync(out + (size_t)i * out_pitch + off, c->slot_out[slot] + (size_t)i * pitch, cur, cudaMemcpyDeviceToHost, s);
+        } else {
+            e = cudaMemcpy2DAsync(out + off, out_pitch, c->slot_out[slot], pitch, cur, pl.rows, cudaMemcpyDeviceToHost, s);
+        }
         if (e != cudaSuccess) rc = fail_cuda(e, "device-to-host slice copy");
     }
     // drain every slot even after a failure: the caller's buffers must not be touched after we return

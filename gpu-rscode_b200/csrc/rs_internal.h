@@ -24,6 +24,8 @@ struct RowGroup {
     int row0 = 0;       // first output row of this group
     int nrows = 0;      // 1..8
     int width = 4;      // bytes per table entry: 4 (<= 4 rows) or 8 (<= 8 rows)
+    int xor_row = -1;   // >= 0: this group's launch ALSO writes output row xor_row (= row0 - 1), whose coefficients
+                        // are all 1, as the plain XOR of the inputs (the peeled row has no table entries)
     uint32_t *d_tab = nullptr;   // points into Plan::d_tabs
     size_t tab_words = 0;        // kpad * 2 * 16 * width / 4
 };
@@ -41,6 +43,7 @@ struct Plan {
     uint32_t *d_tabs = nullptr;   // all groups back to back
     size_t tabs_bytes = 0;
     bool valid = false;
+    bool peeled = false;          // row 0 is all ones and is produced by grp[0] as a XOR row (encode plans, p % 8 == 5)
 };
 
 struct Tuning {
@@ -104,6 +107,14 @@ cudaError_t launch_matmul_fat(const RowGroup &g, int k, const uint8_t *in, size_
                               size_t out_pitch, size_t nvec, const DeviceInfo &dev, int max_blocks, int threads,
                               cudaStream_t s);
 
+
+// ---- gf_matmul_fat_ua_sm100.cu -------------------------------------------------------------------
+// The same kernel for rows of ANY alignment (aligned vector accesses, realigned in registers).  Codes the
+// columns [*vec_lo, *vec_hi) of every row -- more precisely a superset-safe inner range: the caller codes
+// [0, *vec_lo) and [*vec_hi, len) with the byte kernel.  cudaErrorNotSupported: no instance for k / too short.
+cudaError_t launch_matmul_fat_ua(const RowGroup &g, int k, const uint8_t *in, size_t in_pitch, uint8_t *out_g,
+                                 size_t out_pitch, size_t len, const DeviceInfo &dev, int max_blocks, cudaStream_t s,
+                                 size_t *vec_lo, size_t *vec_hi);
 
 // ---- gf_matmul_fat_batch_sm100.cu ---------------------------------------------------------------
 // A batch of n_stripes stripes in ONE launch: fragment j of stripe s at in + s*in_stripe + j*in_pitch.

@@ -93,18 +93,36 @@ void plan_free(Plan &pl)
     pl = Plan();
 }
 
+// Does peeling an all-ones row 0 pay?  Only when it lowers the width class of a launch: rows % 8 == 5 turns
+// the 64-bit-entry group of five rows into four looked-up rows on 32-bit entries (one shared-memory wavefront per
+// lookup instead of two) plus the XOR row.  For <= 4 rows it would only add instructions.
+static bool peel_pays(int rows) { return rows % 8 == 5; }
+
 // Allocate a plan for `rows` x k; rows are cut into groups of 8 (64-bit table entries) with a last
-// group of <= 4 rows using 32-bit entries.
-int plan_alloc(Plan &pl, int rows, int k)
+// group of <= 4 rows using 32-bit entries.  peel: row 0 is all ones (the caller knows) and is left out of
+// the tables; group 0 then starts at row 1 and its launch also writes row 0 as the XOR of the inputs.
+int plan_alloc(Plan &pl, int rows, int k, bool peel = false)
 {
     plan_free(pl);
     pl.rows = rows;
     pl.k = k;
     pl.kpad = (k + 7) / 8 * 8;
     pl.ngroups = 0;
+    pl.peeled = peel && peel_pays(rows);
     size_t words = 0;
-    for (int r0 = 0; r0 < rows;) {
+    // with a peeled row the SHORT group comes first (it is the one with 32-bit entries, which the XOR row needs)
+    for (int r0 = pl.peeled ? 1 : 0; r0 < rows;) {
         RowGroup &g = pl.grp[pl.ngroups++];
+        if (pl.peeled && r0 == 1) {
+            g.row0 = 1;
+            g.nrows = 4;
+            g.width = 4;
+            g.xor_row = 0;
+            g.tab_words = (size_t)pl.kpad * 32 * g.width / 4;
+            words += g.tab_words;
+            r0 += g.nrows;
+            continue;
+        }
         const int left = rows - r0;
         g.row0 = r0;
         g.nrows = left > 8 ? 8 : left;
@@ -267,7 +285,14 @@ static int ctx_create(rsgpu_ctx **out, int device, int k, int p, const uint8_t *
         ++c->launches;
     }
     if (p > 0) {
-        if ((rc = plan_alloc(c->enc, p, k)) != RSGPU_OK) return bail(rc);
+        // Row 0 of the generator all ones?  Always for the reference's Vandermonde matrix ((j+1)^0, src/matrix.cu:758);
+        // read off a caller-supplied matrix; never for Cauchy.
+        bool ones0 = !total && generator == RSGPU_GEN_VANDERMONDE;
+        if (total) {
+            ones0 = true;
+            for (int j = 0; j < k; ++j) ones0 = ones0 && total[(size_t)k * k + j] == 1;
+        }
+        if ((rc = plan_alloc(c->enc, p, k, ones0)) != RSGPU_OK) return bail(rc);
         if ((e = cudaMemcpyAsync(c->enc.d_matrix, c->d_total + (size_t)k * k, (size_t)p * k, cudaMemcpyDeviceToDevice, s)) != cudaSuccess)
             return bail(fail_cuda(e, "copy generator"));
         if ((rc = plan_build_tables(c, c->enc, s)) != RSGPU_OK) return bail(rc);

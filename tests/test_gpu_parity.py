@@ -148,6 +148,81 @@ def test_encode_bank_replicated_kernel_vs_oracle(rs, orc, torch, k, p):
     assert n_launch > 0
 
 
+@pytest.mark.parametrize("k,p", [(10, 5), (15, 5), (4, 5), (7, 13), (25, 5), (40, 5), (16, 21)])
+def test_encode_with_peeled_all_ones_row_vs_oracle(rs, orc, torch, k, p):
+    """Five parity rows (p % 8 == 5): row 0 of the generator is all ones ((j+1)^0, src/matrix.cu:758) and is
+    computed as the XOR of the fragments beside four looked-up rows on 32-bit entries.  Every dispatch path must give
+    the oracle's bytes: byte kernel (short / unaligned short), nibble kernel, byte tables (long and forced), the
+    realigning kernel, the batch kernel, per-row destinations, the host pipeline; a caller-supplied matrix with the
+    same rows peels too, a Cauchy generator must not."""
+    st = torch.cuda.current_stream().cuda_stream
+    V = orc.gen_encoding_matrix(p, k)
+    assert (V[0] == 1).all()
+
+    def check(ctx, L, pitch=None, in_off=0, out_off=0, variant=0, Vm=V):
+        data = splitmix64_bytes(3000 + k * 13 + L % 1009, k * L).reshape(k, L)
+        data[:, :min(L, 256)] = np.arange(256, dtype=np.uint8)[None, :min(L, 256)]
+        ctx.set_tuning(variant=variant)
+        got = gpu_encode(torch, ctx, data, pitch=pitch, out_pitch=pitch, in_off=in_off, out_off=out_off)
+        bad = np.argwhere(got != orc.matrix_mul(Vm, data))
+        assert bad.size == 0, f"L={L} pitch={pitch} variant={variant}: first mismatch at {bad[0]}"
+
+    long_ok = k <= 32
+    with rs.RSContext(k, p) as ctx:
+        check(ctx, 1000)                                        # one launch of the byte kernel
+        check(ctx, 70_001, pitch=70_016)                        # nibble kernel + byte tail
+        check(ctx, 40_000, in_off=3, out_off=9)                 # unaligned short: byte kernel
+        check(ctx, 300_000, pitch=300_032, variant=5)           # byte tables forced (k <= 32) or the nibble kernel
+        check(ctx, 300_000, pitch=300_032, variant=1)           # PRMT variant has no peeled instance: DP4A one runs
+        check(ctx, (3 << 20) + 48, pitch=(3 << 20) + 256)       # 2-8 MiB: the TMA kernel steps aside
+        if long_ok and k <= 16:
+            check(ctx, (8 << 20) + 16)                          # long stripe: byte tables by default
+        check(ctx, (1 << 20) + 5, in_off=1, out_off=2)          # realigning kernel (k <= 32), else byte kernel
+        # batch: 6 stripes, stripe-major, ragged length
+        Ls, n = 70_000 + 5, 6
+        sp_in, sp_out = k * 70_016, p * 70_016
+        data = splitmix64_bytes(4000 + k, n * k * Ls).reshape(n, k, Ls)
+        buf = torch.zeros(n * sp_in, dtype=torch.uint8, device="cuda")
+        buf.view(n, k, 70_016)[:, :, :Ls] = to_dev(torch, data)
+        out = torch.full((n * sp_out,), 0xEE, dtype=torch.uint8, device="cuda")
+        ctx.set_tuning(variant=5)
+        ctx.encode_batch(buf, 70_016, sp_in, out, 70_016, sp_out, Ls, n, st)
+        torch.cuda.synchronize()
+        got = out.view(n, p, 70_016)[:, :, :Ls].cpu().numpy()
+        for s_i in range(n):
+            assert (got[s_i] == orc.matrix_mul(V, data[s_i])).all(), f"batch stripe {s_i}"
+        assert bool((out.view(n, p, 70_016)[:, :, Ls:] == 0xEE).all())
+        ctx.set_tuning(variant=0)
+        # one destination pointer per row (same device)
+        L = 100_000 + 16 * 3 + 5
+        data = splitmix64_bytes(5000 + k, k * L).reshape(k, L)
+        rows = [torch.full((L + 64,), 0xEE, dtype=torch.uint8, device="cuda") for _ in range(p)]
+        ctx.encode_rows(to_dev(torch, data), L, rows, L, st)
+        torch.cuda.synchronize()
+        want = orc.matrix_mul(V, data)
+        for i, r in enumerate(rows):
+            assert (r[:L].cpu().numpy() == want[i]).all() and bool((r[L:] == 0xEE).all()), f"row {i}"
+        # host pipeline
+        L = 600_003
+        hd = splitmix64_bytes(6000 + k, k * L).reshape(k, L)
+        hp = np.zeros((p, L), np.uint8)
+        ctx.encode_host(hd, L, hp, L, L, 2)
+        assert (hp == orc.matrix_mul(V, hd)).all()
+    # the same matrix handed in by the caller peels as well (row k of the total matrix is all ones) ...
+    T = orc.gen_total_encoding_matrix(k, p)
+    with rs.RSContext(k, p, total_matrix=T) as ctx:
+        check(ctx, 300_000, pitch=300_032, variant=5)
+    # ... a total matrix whose first parity row is NOT all ones must not (rows swapped: the all-ones row comes second)
+    T2 = T.copy()
+    T2[[k, k + 1]] = T2[[k + 1, k]]
+    with rs.RSContext(k, p, total_matrix=T2) as ctx:
+        check(ctx, 300_000, pitch=300_032, variant=5, Vm=T2[k:])
+    if k + p <= 256:
+        with rs.RSContext(k, p, generator="cauchy") as ctx:
+            C_ = ctx.generator()
+            check(ctx, 300_000, pitch=300_032, variant=5, Vm=C_)
+
+
 @pytest.mark.parametrize("k", [17, 18, 20, 21, 23, 24, 25, 27, 28, 29, 31, 32])
 @pytest.mark.parametrize("p,L", [(4, 150_003), (3, 16 * 40), (1, 16 * 100_000), (2, 16 * 7 + 5), (4, 16 * 777_777)])
 def test_encode_cluster_kernel_vs_oracle(rs, orc, torch, k, p, L):
@@ -173,6 +248,83 @@ def test_encode_pitch_and_misalignment(rs, orc, torch):
         assert (gpu_encode(torch, ctx, data, pitch=10_009, out_pitch=10_011) == want).all()   # odd pitches -> byte path
         assert (gpu_encode(torch, ctx, data, pitch=10_240, out_pitch=10_240, in_off=3) == want).all()
         assert (gpu_encode(torch, ctx, data, pitch=10_240, out_pitch=10_240, out_off=5) == want).all()
+
+
+UNALIGNED_CASES = [
+    # k, p, L, in_pitch - L, out_pitch - L, in_off, out_off
+    (10, 4, (1 << 20) + 3, 0, 0, 0, 0),            # pitch = L odd: the layout of a file's fragments held back to back
+    (10, 4, (3 << 20) + 7, 0, 0, 5, 11),           # bases unaligned too
+    (10, 4, (1 << 20), 16, 16, 8, 4),              # 16-byte pitches, only the bases are off (every row the same shift)
+    (10, 4, (2 << 20) + 1, 1, 2, 15, 1),
+    (4, 2, (5 << 20) + 9, 0, 0, 1, 2),             # all byte tables (fat8)
+    (16, 4, (1 << 20) + 5, 0, 0, 3, 9),            # transposed bit-7 accumulators
+    (15, 5, (1 << 20) + 13, 0, 0, 7, 7),           # padded shape, five parity rows
+    (32, 8, (1 << 20) + 11, 0, 0, 2, 6),           # 64-bit entries, two row halves
+    (24, 3, (1 << 20) + 6, 0, 0, 0, 12),
+    (7, 3, (1 << 20) + 2, 4, 8, 4, 8),             # word-aligned shifts only
+    (12, 9, (1 << 20) + 3, 0, 0, 9, 3),            # two row groups (8 + 1)
+    (9, 4, (1 << 20) + 3, 0, 0, 6, 10),            # odd batch count (3 x 3)
+    (5, 3, 1_048_576 + 480 * 7 + 1, 0, 0, 13, 14),
+]
+
+
+@pytest.mark.parametrize("k,p,L,dpi,dpo,in_off,out_off", UNALIGNED_CASES)
+def test_encode_unaligned_rows_run_the_vector_kernel(rs, orc, torch, k, p, L, dpi, dpo, in_off, out_off):
+    """Rows that are not 16-byte aligned (odd pitch and/or odd base) must stay on the byte-table kernel --
+    aligned 128-bit accesses realigned in registers -- with the byte kernel only for the head and the tail; every
+    byte equals the oracle's and nothing outside the output rows is touched."""
+    data = splitmix64_bytes(900 + k + L % 97, k * L).reshape(k, L)
+    want = orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)
+    pi, po = L + dpi, L + dpo
+    buf = torch.zeros(k * pi + in_off + 64, dtype=torch.uint8, device="cuda")
+    buf[in_off:in_off + k * pi].view(k, pi)[:, :L] = to_dev(torch, data)
+    out = torch.full((p * po + out_off + 64,), 0xEE, dtype=torch.uint8, device="cuda")
+    with rs.RSContext(k, p) as ctx:
+        n0 = ctx.launch_count()
+        ctx.encode(buf.data_ptr() + in_off, pi, out.data_ptr() + out_off, po, L, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        groups = (p + 7) // 8
+        assert ctx.launch_count() - n0 == 3 * groups, "expected vector kernel + head + tail per row group"
+        # the byte kernel alone (variant 6) gives the same bytes
+        out6 = torch.full_like(out, 0xEE)
+        ctx.set_tuning(variant=6)
+        n0 = ctx.launch_count()
+        ctx.encode(buf.data_ptr() + in_off, pi, out6.data_ptr() + out_off, po, L, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        assert ctx.launch_count() - n0 == groups
+    res = out[out_off:out_off + p * po].view(p, po)
+    got = res[:, :L].cpu().numpy()
+    bad = np.argwhere(got != want)
+    assert bad.size == 0, f"first mismatch at row/byte {bad[0]} of {len(bad)}"
+    assert bool((out[:out_off] == 0xEE).all()) and bool((out[out_off + p * po:] == 0xEE).all())
+    if po > L:
+        assert bool((res[:-1, L:] == 0xEE).all())
+    assert torch.equal(out, out6)
+
+
+def test_encode_unaligned_large_stripe_and_decode(rs, orc, torch):
+    """A long stripe with pitch = L odd (RS(10,14), 64 MiB + 3 per fragment): encode and 4-erasure decode through the
+    realigning kernel; oracle on sampled windows of every row, full round trip on the device."""
+    k, p, L = 10, 4, (64 << 20) + 3
+    st = torch.cuda.current_stream().cuda_stream
+    data = torch.randint(0, 256, (k * L + 1,), dtype=torch.uint8, device="cuda")[1:]      # base 1 byte off
+    par = torch.empty(p * L + 7, dtype=torch.uint8, device="cuda")[7:]
+    V = orc.gen_encoding_matrix(p, k)
+    with rs.RSContext(k, p) as ctx:
+        ctx.encode(data.data_ptr(), L, par.data_ptr(), L, L, st)
+        torch.cuda.synchronize()
+        d2, p2 = data.view(k, L), par.view(p, L)
+        rng = np.random.default_rng(3)
+        for c0 in [0, L - 70_000] + [int(x) for x in rng.integers(0, L - 70_000, 12)]:
+            want = orc.matrix_mul(V, d2[:, c0:c0 + 70_000].cpu().numpy())
+            assert (p2[:, c0:c0 + 70_000].cpu().numpy() == want).all(), f"window at {c0}"
+        order = [10, 11, 12, 13, 4, 5, 6, 7, 8, 9]
+        ctx.set_survivors(order)
+        surv = torch.cat([p2, d2[4:]], dim=0).contiguous().view(-1)                      # k x L, pitch L (odd)
+        out = torch.empty(4 * L + 5, dtype=torch.uint8, device="cuda")[5:]
+        ctx.decode_erased(surv.data_ptr(), L, out.data_ptr(), L, L, st)
+        torch.cuda.synchronize()
+        assert torch.equal(out.view(4, L), d2[:4])
 
 
 def test_encode_overwrites_and_zero_len(rs, torch):

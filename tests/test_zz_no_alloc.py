@@ -53,6 +53,26 @@ def test_noalloc_matches_context_encode_two_calls_in_a_row(env):
     assert bool((got == want).all())
 
 
+def test_noalloc_reaches_the_fast_kernels_and_matches_the_oracle(env):
+    """16-byte aligned stripes long enough for the kernels that expand the shared array's product tables into
+    their own shared-memory tables (byte tables from 8 MiB per fragment, the TMA-fed kernel from 2 MiB), called
+    back to back with different codes, so a stale table entry left by the previous call would show.  Compared
+    with the context-based rsgpu_encode bit for bit and, on a window, with the CPU oracle directly."""
+    torch, rs = env
+    from oracle_lib import Oracle
+    orc = Oracle()
+    st = torch.cuda.current_stream().cuda_stream
+    for k, p, L, seed in [(10, 4, (8 << 20) + 16, 11), (32, 8, 4 << 20, 12), (16, 4, (8 << 20) + 32, 13), (10, 4, 4 << 20, 14),
+                          (12, 5, (8 << 20) + 3, 15)]:
+        got, want = _encode_both(torch, rs, k, p, L, seed=seed)
+        assert bool((got == want).all()), (k, p, L)
+        g = torch.Generator(device="cuda").manual_seed(seed)
+        data = torch.randint(0, 256, (k, L), dtype=torch.uint8, device="cuda", generator=g)     # the same bytes _encode_both drew
+        for c0 in (0, L - 4096, (L // 2) & ~15):
+            ref = orc.matrix_mul(orc.gen_encoding_matrix(p, k), data[:, c0:c0 + 4096].cpu().numpy())
+            assert (got[:, c0:c0 + 4096].cpu().numpy() == ref).all(), (k, p, L, c0)
+
+
 def test_noalloc_rejects_oversized_codes_and_bad_arguments(env):
     torch, rs = env
     d = torch.zeros((40, 256), dtype=torch.uint8, device="cuda")
