@@ -32,6 +32,16 @@ __host__ __device__ constexpr int fat_threads(int W, int JB, bool T7)
     return JB <= 2 ? 768 : (JB <= 5 ? 512 : (JB <= 8 ? 384 : 256));
 }
 
+// block size of the instances that also produce the peeled all-ones row (four more accumulator registers): one
+// size down where ptxas -v showed spills at the regular size (padded shapes with transposed bit-7 terms or six and
+// more batches, and the 3 x 3 shape)
+__host__ __device__ constexpr int fat_threads_x(int W, int JB, int KB, bool T7, bool PAD, bool XR)
+{
+    int t = fat_threads(W, JB, T7);
+    if (XR && ((PAD && (T7 || KB >= 6)) || (JB == 3 && KB == 3))) t -= 128;
+    return t;
+}
+
 __device__ __forceinline__ uint4 ldg_stream(const uint8_t *p)
 {
     uint4 v;

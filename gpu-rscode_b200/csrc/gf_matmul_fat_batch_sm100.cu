@@ -93,7 +93,7 @@ __device__ __forceinline__ void do_column_b(uint4 (&buf0)[JB], uint4 (&buf1)[JB]
 }
 
 template <int W, int JB, int KB, bool PF, bool T7, bool PAD, bool XR>
-__global__ void __launch_bounds__(fat_threads(W, JB, T7), 1)
+__global__ void __launch_bounds__(fat_threads_x(W, JB, KB, T7, PAD, XR), 1)
 k_gf_matmul_fat_batch(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
                       const uint32_t *__restrict__ tab, int nrows, BatchGeom g, int k)
 {
@@ -144,7 +144,7 @@ FatBatchKernel make_fat_batch()
 {
     constexpr int K = JB * KB;
     constexpr bool PF = fat_use_prefetch(K), T7 = fat_use_t7(W, K);
-    return FatBatchKernel{k_gf_matmul_fat_batch<W, JB, KB, PF, T7, PAD, XR>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
+    return FatBatchKernel{k_gf_matmul_fat_batch<W, JB, KB, PF, T7, PAD, XR>, fat_threads_x(W, JB, KB, T7, PAD, XR), Map<K>::BYTES + 256};
 }
 
 // the same shape per k as the single-stripe kernel (RSGPU_FAT_SHAPES, gf_matmul_fat.cuh)

@@ -74,7 +74,7 @@ __device__ __forceinline__ void do_column(uint4 (&buf0)[JB], uint4 (&buf1)[JB], 
 }
 
 template <int W, int JB, int KB, bool PF, bool T7, bool PAD, bool XR>
-__global__ void __launch_bounds__(fat_threads(W, JB, T7), 1)
+__global__ void __launch_bounds__(fat_threads_x(W, JB, KB, T7, PAD, XR), 1)
 k_gf_matmul_fat(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
                 const uint32_t *__restrict__ tab, int nrows, size_t nvec, int k)
 {
@@ -126,7 +126,7 @@ FatKernel make_fat()
     // (RS(10,14) 0.930 -> 0.754, RS(12,16) 0.878 -> 0.639).
     constexpr int K = JB * KB;
     constexpr bool T7 = fat_use_t7(W, K);
-    return FatKernel{k_gf_matmul_fat<W, JB, KB, PF, T7, PAD, XR>, fat_threads(W, JB, T7), Map<K>::BYTES + 256};
+    return FatKernel{k_gf_matmul_fat<W, JB, KB, PF, T7, PAD, XR>, fat_threads_x(W, JB, KB, T7, PAD, XR), Map<K>::BYTES + 256};
 }
 
 template <int W, bool XR = false>

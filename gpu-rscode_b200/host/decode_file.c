@@ -77,7 +77,6 @@ void decode_file(char *inFile, char *confFile, char *outFile, int gridDimXSize, 
     }
 
     const int gpu_budget = rs_file_gpu_budget(md.total_size);
-    rs_limit_visible_gpus(gpu_budget); /* before the first CUDA call: start-up cost scales with visible GPUs */
 
     int maxGrid = 65535;
     struct timespec ts0, ts1;

@@ -40,7 +40,6 @@ void encode_file(char *fileName, int nativeBlockNum, int parityBlockNum, int gri
     const long long chunk = rs_chunk_size(totalSize, k);
 
     const int gpu_budget = rs_file_gpu_budget(totalSize);
-    rs_limit_visible_gpus(gpu_budget); /* before the first CUDA call: start-up cost scales with visible GPUs */
 
     int maxGrid = 65535;
     struct timespec ts0, ts1;

@@ -14,6 +14,7 @@
 
 #include "decode.h"
 #include "encode.h"
+#include "rs_host.h"
 
 static void show_help_info(void)
 {
@@ -63,11 +64,13 @@ int main(int argc, char *argv[])
     case ENCODE:
         assert(k != 0);
         assert(n != 0);
+        rs_cli_prepare_gpus(inFile, 0); /* our own process: start CUDA on the GPUs this job will use, not on all */
         encode_file(inFile, k, n - k, grid, streams);
         break;
     case DECODE:
         assert(inFile != NULL);
         assert(confFile != NULL);
+        rs_cli_prepare_gpus(inFile, 1);
         decode_file(inFile, confFile, outFile, grid, streams);
         break;
     default:

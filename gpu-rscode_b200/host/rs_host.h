@@ -34,7 +34,7 @@ void rs_free_conf(rs_conf *conf);
 int rs_plan_gpus(size_t len, int visible);
 void rs_partition(size_t len, int parts, int g, size_t *off, size_t *n);
 int rs_file_gpu_budget(long long bytes);
-void rs_limit_visible_gpus(int n);
+void rs_cli_prepare_gpus(const char *file, int decode); /* RS binary only: narrows CUDA_VISIBLE_DEVICES to the job's GPU budget */
 
 /* ---- stream.c : streaming slab pipeline  file -> pinned ring -> GPU(s) -> files ---- */
 typedef struct {

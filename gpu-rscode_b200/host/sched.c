@@ -7,6 +7,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/stat.h>
 
 #include "rs_host.h"
 
@@ -50,8 +51,10 @@ int rs_file_gpu_budget(long long bytes)
 
 /* Narrow CUDA_VISIBLE_DEVICES to the first `n` devices (of the user's list if there is one) so that the
  * CUDA start-up of this process only pays for the GPUs it will use.  Only effective before the first
- * CUDA call of the process; harmless afterwards (the pipeline caps its GPU count anyway). */
-void rs_limit_visible_gpus(int n)
+ * CUDA call of the process.  This edits the process environment, so it is called by the RS command line
+ * (main.c, a process of our own) and NEVER from encode_file / decode_file: a program that embeds the library
+ * keeps its environment, and the library simply creates no context on GPUs beyond the job's budget. */
+static void rs_limit_visible_gpus(int n)
 {
     const char *cur = getenv("CUDA_VISIBLE_DEVICES");
     char buf[1024];
@@ -81,4 +84,28 @@ void rs_limit_visible_gpus(int n)
     }
     if (buf[0])
         setenv("CUDA_VISIBLE_DEVICES", buf, 1);
+}
+
+/* Command-line helper (main.c): size the job from the file (encode) or from "<file>.METADATA" (decode) and
+ * narrow the visible GPUs to its budget before CUDA starts.  Errors are left to encode_file / decode_file. */
+void rs_cli_prepare_gpus(const char *file, int decode)
+{
+    long long bytes = -1;
+    if (!file) return;
+    if (decode) {
+        const size_t nlen = strlen(file) + 32;
+        char *name = malloc(nlen);
+        if (!name) return;
+        snprintf(name, nlen, "%s.METADATA", file);
+        FILE *fp = fopen(name, "rb");
+        free(name);
+        if (fp) {
+            if (fscanf(fp, "%lld", &bytes) != 1) bytes = -1;
+            fclose(fp);
+        }
+    } else {
+        struct stat sb;
+        if (stat(file, &sb) == 0) bytes = (long long)sb.st_size;
+    }
+    if (bytes >= 0) rs_limit_visible_gpus(rs_file_gpu_budget(bytes));
 }

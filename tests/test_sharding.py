@@ -114,8 +114,9 @@ def test_world2_gloo_stripe_sharding_matches_single_process():
 
 
 def test_file_gpu_budget_and_visible_device_narrowing():
-    """host/sched.c: one GPU per 32 GiB of file unless RS_GPUS says otherwise; CUDA_VISIBLE_DEVICES is
-    narrowed to the first n (of the user's list if any).  Run in a child: it edits the environment."""
+    """host/sched.c: one GPU per 32 GiB of file unless RS_GPUS says otherwise.  The RS command line (and only it:
+    encode_file / decode_file leave the environment of an embedding program alone) narrows CUDA_VISIBLE_DEVICES
+    to the first n devices (of the user's list if any) before CUDA starts.  Run in a child: it edits the environment."""
     import subprocess
     import sys
     code = r'''
@@ -130,11 +131,21 @@ assert H.rs_file_gpu_budget(32 << 30) == 1 and H.rs_file_gpu_budget((32 << 30) +
 assert H.rs_file_gpu_budget(1 << 40) == 32
 libc.setenv(b"RS_GPUS", b"8", 1)
 assert H.rs_file_gpu_budget(10) == 8
-H.rs_limit_visible_gpus(3); assert libc.getenv(b"CUDA_VISIBLE_DEVICES") == b"0,1,2"
-libc.setenv(b"CUDA_VISIBLE_DEVICES", b"4,5,6,7", 1); H.rs_limit_visible_gpus(2)
+import tempfile
+d = tempfile.mkdtemp()
+f = os.path.join(d, "file.bin").encode(); open(f, "wb").write(b"x" * 1000)
+open(f + b".METADATA", "w").write("1000\n2 4\n")
+H.rs_cli_prepare_gpus.argtypes = [ctypes.c_char_p, ctypes.c_int]
+libc.setenv(b"RS_GPUS", b"3", 1)
+H.rs_cli_prepare_gpus(f, 0); assert libc.getenv(b"CUDA_VISIBLE_DEVICES") == b"0,1,2"
+libc.setenv(b"CUDA_VISIBLE_DEVICES", b"4,5,6,7", 1); libc.setenv(b"RS_GPUS", b"2", 1); H.rs_cli_prepare_gpus(f, 1)
 assert libc.getenv(b"CUDA_VISIBLE_DEVICES") == b"4,5"
-libc.setenv(b"CUDA_VISIBLE_DEVICES", b"6", 1); H.rs_limit_visible_gpus(4)
+libc.setenv(b"CUDA_VISIBLE_DEVICES", b"6", 1); libc.setenv(b"RS_GPUS", b"4", 1); H.rs_cli_prepare_gpus(f, 0)
 assert libc.getenv(b"CUDA_VISIBLE_DEVICES") == b"6"
+libc.unsetenv(b"RS_GPUS"); libc.setenv(b"CUDA_VISIBLE_DEVICES", b"0,1,2,3", 1); H.rs_cli_prepare_gpus(f, 0)
+assert libc.getenv(b"CUDA_VISIBLE_DEVICES") == b"0"                     # 1000 bytes: one GPU
+H.rs_cli_prepare_gpus(os.path.join(d, "missing").encode(), 0)          # unknown size: environment untouched
+assert libc.getenv(b"CUDA_VISIBLE_DEVICES") == b"0"
 print("ok")
 '''
     r = subprocess.run([sys.executable, "-c", code, rs.LIB_PATH, rs.HOST_LIB_PATH], stdout=subprocess.PIPE,
