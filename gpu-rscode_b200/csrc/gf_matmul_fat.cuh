@@ -352,7 +352,7 @@ __device__ __forceinline__ void build_block_tables(uint32_t tb, const uint32_t *
     X(8, 4, 2, false) X(9, 3, 3, false) X(10, 5, 2, false) X(11, 3, 4, true) X(12, 3, 4, false)               \
     X(13, 7, 2, true) X(14, 7, 2, false) X(15, 4, 4, true) X(16, 4, 4, false) X(17, 3, 6, true)               \
     X(18, 3, 6, false) X(19, 5, 4, true) X(20, 5, 4, false) X(21, 4, 6, true) X(22, 4, 6, true)               \
-    X(23, 4, 6, true) X(24, 4, 6, false) X(25, 7, 4, true) X(26, 7, 4, true) X(27, 7, 4, true) X(28, 7, 4, false)      \
+    X(23, 4, 6, true) X(24, 4, 6, false) X(26, 7, 4, true) X(27, 7, 4, true)      \
     X(29, 4, 8, true) X(30, 4, 8, true) X(31, 4, 8, true) X(32, 4, 8, false)
 
 // which instances use the L2 prefetch / the transposed bit-7 accumulation (measurements: make_fat)

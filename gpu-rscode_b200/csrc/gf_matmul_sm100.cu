@@ -289,6 +289,25 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
         if (e != cudaErrorNotSupported) return e;
     }
 
+    // variant 9: the multi-pass kernel (gf_matmul_fat_mp_sm100.cu) for k > 14 -- the fragments taken 14 at a time through
+    // all-byte-table passes, partial parities kept in registers across the table rebuilds.  Measured SLOWER than the
+    // nibble kernels it was meant to replace for k >= 25 (RS(28,32) 0.55 vs 0.67, RS(64,68) 0.48 vs 0.64, RS(128,132)
+    // 0.42 vs 0.56 of the HBM peak), so it is never chosen automatically; kept as a tested, selectable experiment
+    // (DESIGN.md section 4.1 h).  It codes whole block steps; the columns behind them go down the ordinary path.
+    if (nvec && tune.variant == 9 && k > 14) {
+        size_t done = 0;
+        cudaError_t e = launch_matmul_fat_mp(g, k, in, in_pitch, out_g, out_pitch, nvec, dev, tune.max_blocks, s, &done);
+        if (e == cudaSuccess) {
+            if (launches) ++*launches;
+            if (done * 16 >= len) return cudaSuccess;
+            Tuning rest = tune;
+            rest.variant = 6;
+            return launch_matmul_group(g, k, kpad, in + done * 16, in_pitch, out + done * 16, out_pitch, len - done * 16, rest, dev, s,
+                                       launches);
+        }
+        if (e != cudaErrorNotSupported) return e;
+    }
+
     // variant 0 (default): the bank-replicated kernel when an instance exists for this k and the stripe
     // is long enough to pay for building its tables (one 227 KiB fill per SM: measured break-even
     // on B200 at 4-8 MiB per fragment for RS(10,14)); 5 forces it, 6 forbids it

@@ -116,6 +116,13 @@ cudaError_t launch_matmul_fat_ua(const RowGroup &g, int k, const uint8_t *in, si
                                  size_t out_pitch, size_t len, const DeviceInfo &dev, int max_blocks, cudaStream_t s,
                                  size_t *vec_lo, size_t *vec_hi);
 
+// ---- gf_matmul_fat_mp_sm100.cu -------------------------------------------------------------------
+// Byte tables in passes of 14 fragments, partial parities kept in registers (k >= 25).  Codes the first *done_vec
+// 16-byte columns (whole block steps); cudaErrorNotSupported when the stripe is shorter than one step.
+cudaError_t launch_matmul_fat_mp(const RowGroup &g, int k, const uint8_t *in, size_t in_pitch, uint8_t *out_g,
+                                 size_t out_pitch, size_t nvec, const DeviceInfo &dev, int max_blocks, cudaStream_t s,
+                                 size_t *done_vec);
+
 // ---- gf_matmul_fat_batch_sm100.cu ---------------------------------------------------------------
 // A batch of n_stripes stripes in ONE launch: fragment j of stripe s at in + s*in_stripe + j*in_pitch.
 // cudaErrorNotSupported when there is no instance for k (the caller then launches per stripe).

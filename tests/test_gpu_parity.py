@@ -121,7 +121,7 @@ def test_encode_vs_oracle(rs, orc, torch, k, p, L):
     assert (got == want).all()
 
 
-@pytest.mark.parametrize("variant", [0, 1, 5, 6, 7])  # auto, nibble+PRMT, byte tables, nibble+DP4A, nibble fed by TMA
+@pytest.mark.parametrize("variant", [0, 1, 5, 6, 7, 9])  # auto, nibble+PRMT, byte tables, nibble+DP4A, nibble fed by TMA, multi-pass
 @pytest.mark.parametrize("k,p,L", [(10, 4, 200_000), (32, 8, 50_000), (11, 3, 40_001), (13, 5, 160_000), (19, 2, 64_000), (23, 8, 32_000),
                                      (16, 4, 70_000 * 16), (5, 2, 4096 * 16 + 48), (4, 8, 100_000)])
 def test_encode_variants_vs_oracle(rs, orc, torch, variant, k, p, L):
@@ -132,7 +132,7 @@ def test_encode_variants_vs_oracle(rs, orc, torch, variant, k, p, L):
     assert (got == orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)).all()
 
 
-@pytest.mark.parametrize("k", [2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22, 23, 24, 27, 29, 31, 32])
+@pytest.mark.parametrize("k", list(range(2, 33)))
 @pytest.mark.parametrize("p", [1, 4, 5, 8])
 def test_encode_bank_replicated_kernel_vs_oracle(rs, orc, torch, k, p):
     """variant 5 forces the byte-table kernel (fat8 / fat7 / nibble mix depends on k) at a small size."""
@@ -146,6 +146,49 @@ def test_encode_bank_replicated_kernel_vs_oracle(rs, orc, torch, k, p):
         n_launch = ctx.launch_count()
     assert (got == orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)).all()
     assert n_launch > 0
+
+
+@pytest.mark.parametrize("k,p", [(15, 4), (25, 4), (28, 4), (29, 3), (32, 8), (33, 1), (40, 5), (64, 4), (100, 6), (128, 2), (255, 4), (42, 13)])
+def test_encode_multipass_kernel_vs_oracle(rs, orc, torch, k, p):
+    """variant 9 forces the multi-pass byte-table kernel (fragments taken 14 at a time, partial parities in registers
+    across the table rebuilds): one block step exactly, several steps plus a remainder that goes down the ordinary
+    path, a ragged tail; last pass short (k % 14 != 0), one full pass plus one fragment, k = 255."""
+    V = orc.gen_encoding_matrix(p, k)
+    with rs.RSContext(k, p) as ctx:
+        ctx.set_tuning(variant=9)
+        for L in (24_576, 3 * 24_576 + 16 * 37 + 5, 200_000):
+            data = splitmix64_bytes(7000 + k * 3 + p + L % 13, k * L).reshape(k, L)
+            data[:, :256] = np.arange(256, dtype=np.uint8)[None, :]
+            pitch = (L + 255) // 256 * 256
+            n0 = ctx.launch_count()
+            got = gpu_encode(torch, ctx, data, pitch=pitch, out_pitch=pitch)
+            assert ctx.launch_count() > n0
+            bad = np.argwhere(got != orc.matrix_mul(V, data))
+            assert bad.size == 0, f"L={L}: first mismatch at {bad[0]} of {len(bad)}"
+
+
+def test_encode_multipass_kernel_long_stripe(rs, orc, torch):
+    """The multi-pass kernel (variant 9) on a long stripe, many block steps per SM: oracle on sampled windows, and the
+    same bytes as the nibble kernel (variant 6)."""
+    k, p, L = 40, 4, (8 << 20) + 16 * 100 + 7
+    pitch = (L + 255) // 256 * 256
+    st = torch.cuda.current_stream().cuda_stream
+    data = torch.randint(0, 256, (k, pitch), dtype=torch.uint8, device="cuda")
+    out = torch.full((p, pitch), 0xEE, dtype=torch.uint8, device="cuda")
+    out6 = torch.full((p, pitch), 0xEE, dtype=torch.uint8, device="cuda")
+    V = orc.gen_encoding_matrix(p, k)
+    with rs.RSContext(k, p) as ctx:
+        ctx.set_tuning(variant=9)
+        ctx.encode(data, pitch, out, pitch, L, st)
+        ctx.set_tuning(variant=6)
+        ctx.encode(data, pitch, out6, pitch, L, st)
+        torch.cuda.synchronize()
+    assert torch.equal(out, out6)
+    assert bool((out[:, L:] == 0xEE).all())
+    rng = np.random.default_rng(5)
+    for c0 in [0, L - 50_000] + [int(x) for x in rng.integers(0, L - 50_000, 6)]:
+        want = orc.matrix_mul(V, data[:, c0:c0 + 50_000].cpu().numpy())
+        assert (out[:, c0:c0 + 50_000].cpu().numpy() == want).all(), f"window at {c0}"
 
 
 @pytest.mark.parametrize("k,p", [(10, 5), (15, 5), (4, 5), (7, 13), (25, 5), (40, 5), (16, 21)])
