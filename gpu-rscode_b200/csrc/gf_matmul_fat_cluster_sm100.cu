@@ -152,7 +152,10 @@ k_gf_matmul_fat_cluster(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t
             acc.a[i] = 0;
             acc.t[i] = 0;
         }
-        ColumnBatchesC<W, KH, JB, KB, 0, PF, T7, XB>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1, k_local);
+        // lanes of the last, partial warp that lie past the end of the stripe take part in the exchange but must not
+        // load: their q was never set for this column (k_eff = 0 makes every load of the column a zero fill)
+        const int k_eff = v < nvec ? k_local : 0;
+        ColumnBatchesC<W, KH, JB, KB, 0, PF, T7, XB>::run(buf0, buf1, q, in_pitch, in, vn, nvec, lane_base, tb, acc, pf0, pf1, k_eff);
 
         // 4x4 byte transpose into row order: r[row][word]
         uint32_t r[4][4];
