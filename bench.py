@@ -325,6 +325,13 @@ def side_leg(torch, rs, name, local_rank, stream, peak, steps, seed, sustained_s
                     "input_gbs": k * L * steps / (total_ms / 1e3) / 1e9, "achieved": ach, "peak": peak, "unit": "GB/s",
                     "frac": ach / peak, "algorithmic_bytes_per_launch": algo,
                     "launches_per_step": (ctx.launch_count() - l0) / steps})
+        try:      # DRAM bytes per launch of this leg's kernel from its ncu --set full capture (profiles/traffic.json)
+            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(name)
+            if tr:
+                leg["traffic"] = tr["dram_bytes_per_launch"]
+                leg["traffic_source"] = tr.get("source")
+        except Exception:
+            pass
         if mode == "decode":
             leg["step"] = "rsgpu_set_survivors (GPU Gauss-Jordan inverse + tables, blocks) + rsgpu_decode_erased, every step"
         if sustained_s > 0:
