@@ -94,6 +94,41 @@ k_gf_matmul(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict
     }
 }
 
+// One output row whose coefficients are all 1 -- the single parity of RS(k, k+1), or the one lost native of a stripe
+// that still has parity row 0 (the commonest repair there is): the row is the XOR of the k inputs, no tables, no
+// lookups.  U loads in flight per thread, 8 blocks of 256 threads per SM: plain HBM streaming.
+template <int U>
+__global__ void __launch_bounds__(256)
+k_xor_rows(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, int k, size_t nvec)
+{
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += stride) {
+        uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+        const uint8_t *q = in + v * 16;
+        int j = 0;
+        for (; j + U <= k; j += U) {
+            uint4 d[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) d[u] = ldg_stream(q + (size_t)(j + u) * in_pitch);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                acc.x ^= d[u].x;
+                acc.y ^= d[u].y;
+                acc.z ^= d[u].z;
+                acc.w ^= d[u].w;
+            }
+        }
+        for (; j < k; ++j) {
+            const uint4 d = ldg_stream(q + (size_t)j * in_pitch);
+            acc.x ^= d.x;
+            acc.y ^= d.y;
+            acc.z ^= d.z;
+            acc.w ^= d.w;
+        }
+        stg_stream(out + v * 16, acc);
+    }
+}
+
 // Byte-granular fallback: heads/tails shorter than 16 bytes and buffers that are not 16-byte aligned
 // (the reference's matrix_mul<unsigned char>, src/matrix.cu:335-407, used whenever size % 8 != 0).
 template <int W>
@@ -289,6 +324,20 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
         if (e != cudaErrorNotSupported) return e;
     }
 
+    // a single all-ones row: XOR of the inputs, no lookups (the byte tail below still uses the tables, which exist)
+    bool xor_done = false;
+    if (nvec && g.all_ones && g.nrows == 1 && !xr && tune.variant == 0) {
+        int occ = 0;
+        cudaError_t e = prepare_launch(dev, (const void *)k_xor_rows<8>, 256, 0, &occ);
+        if (e != cudaSuccess) return e;
+        size_t want = (nvec + 255) / 256, cap = (size_t)dev.sm_count * occ;
+        if (tune.max_blocks > 0 && (size_t)tune.max_blocks < cap) cap = tune.max_blocks;
+        k_xor_rows<8><<<(unsigned)(want < cap ? want : cap), 256, 0, s>>>(in, in_pitch, out_g, k, nvec);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if (launches) ++*launches;
+        xor_done = true;
+    }
+
     // variant 9: the multi-pass kernel (gf_matmul_fat_mp_sm100.cu) for k > 14 -- the fragments taken 14 at a time through
     // all-byte-table passes, partial parities kept in registers across the table rebuilds.  Measured SLOWER than the
     // nibble kernels it was meant to replace for k >= 25 (RS(28,32) 0.55 vs 0.67, RS(64,68) 0.48 vs 0.64, RS(128,132)
@@ -311,7 +360,7 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
     // variant 0 (default): the bank-replicated kernel when an instance exists for this k and the stripe
     // is long enough to pay for building its tables (one 227 KiB fill per SM: measured break-even
     // on B200 at 4-8 MiB per fragment for RS(10,14)); 5 forces it, 6 forbids it
-    bool done_vec = false;
+    bool done_vec = xor_done;
     // variant 8: the cluster kernel for k = 17..32 (fragments split over two CTAs, partial parities exchanged
     // through distributed shared memory).  Measured SLOWER than the single-CTA kernel on every such code
     // (RS(24,28) 0.73 vs 0.81, RS(20,24) 0.67 vs 0.87, RS(32,36) 0.66 vs 0.71 of the HBM peak), so it is never

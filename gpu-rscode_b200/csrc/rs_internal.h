@@ -24,6 +24,7 @@ struct RowGroup {
     int row0 = 0;       // first output row of this group
     int nrows = 0;      // 1..8
     int width = 4;      // bytes per table entry: 4 (<= 4 rows) or 8 (<= 8 rows)
+    bool all_ones = false;   // nrows == 1 and every coefficient is 1: the row is the plain XOR of the inputs (no lookups)
     int xor_row = -1;   // >= 0: this group's launch ALSO writes output row xor_row (= row0 - 1), whose coefficients
                         // are all 1, as the plain XOR of the inputs (the peeled row has no table entries)
     uint32_t *d_tab = nullptr;   // points into Plan::d_tabs

@@ -131,6 +131,7 @@ int plan_alloc(Plan &pl, int rows, int k, bool peel = false)
         words += g.tab_words;
         r0 += g.nrows;
     }
+    if (peel && rows == 1) pl.grp[0].all_ones = true;   // RS(k, k+1): the one parity row is the XOR of the fragments
     pl.tabs_bytes = words * 4;
     CK(cudaMalloc(&pl.d_matrix, (size_t)rows * k));
     CK(cudaMalloc(&pl.d_tabs, pl.tabs_bytes));
@@ -486,8 +487,17 @@ int rsgpu_set_survivors(rsgpu_ctx *c, const int *idx)
                            c->d_flag, c->gf, s));
     ++c->launches;
     int flag = 0;
+    uint8_t one_row[256];
     CK(cudaMemcpyAsync(&flag, c->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+    // one native lost: if the row that rebuilds it is all ones (parity row 0 among the survivors, the others natives) the
+    // decode is a plain XOR of the survivors -- look at the row while we wait for the flag anyway
+    if (c->n_erased == 1) CK(cudaMemcpyAsync(one_row, ds.erased.d_matrix, (size_t)k, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
+    if (c->n_erased > 0) {
+        bool ones = c->n_erased == 1 && !flag;
+        for (int j = 0; ones && j < k; ++j) ones = one_row[j] == 1;
+        ds.erased.grp[0].all_ones = ones;
+    }
     ds.readers.reset();                           // the set-up stream has drained: nobody reads the old tables any more
     if (flag) return fail_msg(RSGPU_ESINGULAR, "the chosen survivors give a singular matrix");
     ds.full.valid = false;                        // matrix there, tables not yet

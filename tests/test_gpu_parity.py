@@ -589,6 +589,40 @@ def test_decode_on_several_streams_right_after_set_survivors(rs, torch):
                 assert torch.equal(out, data), f"round {rnd}, stream {i}"
 
 
+@pytest.mark.parametrize("k", [1, 2, 7, 10, 16, 33, 200])
+def test_single_all_ones_row_is_a_plain_xor(rs, orc, torch, k):
+    """One output row whose coefficients are all 1 runs the XOR kernel (no tables): the parity of RS(k, k+1), and the one
+    lost native of a stripe that still has parity row 0.  The same stripe with parity row 1 instead takes the table
+    kernels; all of it against the oracle, aligned and unaligned, with a ragged tail."""
+    st = torch.cuda.current_stream().cuda_stream
+    for L, pitch in ((100_000 + 5, 100_016), (70_001, 70_001), (5, 16)):
+        data = splitmix64_bytes(9000 + k + L, k * L).reshape(k, L)
+        with rs.RSContext(k, 1) as ctx:
+            got = gpu_encode(torch, ctx, data, pitch=pitch, out_pitch=pitch)
+        assert (got == orc.matrix_mul(orc.gen_encoding_matrix(1, k), data)).all()
+    if k < 2 or k > 100:
+        return
+    p, L = 3, 300_000 + 16 * 3 + 7
+    pitch = (L + 255) // 256 * 256
+    data = splitmix64_bytes(9100 + k, k * L).reshape(k, L)
+    V = orc.gen_encoding_matrix(p, k)
+    frags = np.concatenate([data, orc.matrix_mul(V, data)], axis=0)
+    lost = k // 2
+    for par in (k, k + 1):                      # parity row 0 (all ones -> XOR), parity row 1 (tables)
+        order = list(range(k))
+        order[lost] = par
+        surv = torch.zeros((k, pitch), dtype=torch.uint8, device="cuda")
+        surv[:, :L] = to_dev(torch, frags[order])
+        out = torch.full((1, pitch), 0xEE, dtype=torch.uint8, device="cuda")
+        with rs.RSContext(k, p) as ctx:
+            ctx.set_survivors(order)
+            assert ctx.erased() == [lost]
+            ctx.decode_erased(surv, pitch, out, pitch, L, st)
+            torch.cuda.synchronize()
+        assert (out[0, :L].cpu().numpy() == data[lost]).all(), f"parity {par}"
+        assert bool((out[0, L:] == 0xEE).all())
+
+
 def test_gpu_encode_then_gpu_decode_all_double_erasures_rs46(rs, torch):
     k, p, L = 4, 2, 3_001
     data = splitmix64_bytes(9, k * L).reshape(k, L)
