@@ -664,6 +664,8 @@ def main():
                     e2e["peak"] = pk["encode_input_ceiling_gbs"]
                     e2e["frac"] = e2e["value"] / pk["encode_input_ceiling_gbs"]
                     e2e["peak_source"] = pk.get("source")
+                    e2e["peak_note"] = ("the probe (two monolithic 2 GiB streams per GPU) is a floor of what the box can deliver: "
+                                        "the pipeline's interleaved slices measure above it at N >= 2")
             except Exception:
                 pass
         if rank == 0:   # the host-path result: the oracle on windows, and the device-path result of the same input

@@ -535,7 +535,14 @@ int rsgpu_set_repair(rsgpu_ctx *c, const int *survivors, const int *wanted, int 
     CK(launch_rows_times_matrix(c->d_total, c->d_rows, n_wanted, c->dec_full().d_matrix, k, c->repair.d_matrix, c->gf, s));
     ++c->launches;
     if ((rc = plan_build_tables(c, c->repair, s)) != RSGPU_OK) return rc;
+    uint8_t one_row[256];
+    if (n_wanted == 1) CK(cudaMemcpyAsync(one_row, c->repair.d_matrix, (size_t)k, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
+    {   // one wanted fragment whose repair row is all ones (parity 0 from the natives, a native from the rest + parity 0): XOR
+        bool ones = n_wanted == 1;
+        for (int j = 0; ones && j < k; ++j) ones = one_row[j] == 1;
+        c->repair.grp[0].all_ones = ones;
+    }
     c->repair_readers.reset();
     c->have_repair = true;
     return RSGPU_OK;

@@ -733,7 +733,8 @@ def test_sampled_windows_vs_oracle_large(rs, orc, torch):
 # ---- repair of arbitrary fragments, Cauchy generator ---------------------------
 
 @pytest.mark.parametrize("k,p,lost", [(10, 4, [3, 12]), (10, 4, [0, 1, 10, 13]), (4, 2, [5]), (16, 4, [2, 7, 16, 19]),
-                                      (32, 8, [0, 5, 33, 39, 31, 32, 34, 1])])
+                                      (32, 8, [0, 5, 33, 39, 31, 32, 34, 1]),
+                                      (10, 4, [10]), (10, 4, [4]), (40, 2, [40])])   # one row, all ones: the XOR kernel
 def test_repair_any_fragments_vs_oracle(rs, orc, torch, k, p, lost):
     L = 40_000 + 16
     data = splitmix64_bytes(900 + k, k * L).reshape(k, L)
