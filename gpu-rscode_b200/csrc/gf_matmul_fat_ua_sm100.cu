@@ -22,12 +22,13 @@
 //   * the first 32 and the last < 48 bytes of every row (where an aligned vector would reach outside the row)
 //     go to the byte kernel, as before.
 #include "gf_matmul_fat.cuh"
+#include "gf_realign.cuh"
 
 namespace rsgpu {
 namespace {
 
-constexpr int kHead = 16;       // logical bytes in front of window 0 (keeps every aligned vector inside its row)
-constexpr int kSpan = 30;       // windows stored per warp per step
+constexpr int kHead = kUaHead;
+constexpr int kSpan = kUaSpan;
 
 __host__ __device__ constexpr int fat_threads_ua(int W, int JB, int KB, bool T7)
 {
@@ -38,31 +39,6 @@ __host__ __device__ constexpr int fat_threads_ua(int W, int JB, int KB, bool T7)
     if (W == 4 && t > 512) t = JB <= 2 ? 768 : 512;
     if (JB * KB >= 18) t -= 128;
     return t < 256 ? 256 : t;
-}
-
-__device__ __forceinline__ uint4 shfl_next(const uint4 &v)
-{
-    uint4 r;
-    r.x = __shfl_down_sync(0xffffffffu, v.x, 1);
-    r.y = __shfl_down_sync(0xffffffffu, v.y, 1);
-    r.z = __shfl_down_sync(0xffffffffu, v.z, 1);
-    r.w = __shfl_down_sync(0xffffffffu, v.w, 1);
-    return r;
-}
-
-// bytes [s, s + 16) of the 32-byte pair (o, n); 0 <= s <= 15, the same for every lane of the warp -- and of the
-// grid: s depends on the row only, so the three selectors below are loop-invariant and ptxas keeps them in
-// uniform registers.  Three PRMT stages (shift by 8, by 4, by 0..3 bytes), no predicates: 15 alu instructions.
-__device__ __forceinline__ uint4 realign(const uint4 &o, const uint4 &n, uint32_t s)
-{
-    const uint32_t sa = (s & 8u) ? 0x7654u : 0x3210u;        // take the word two places up
-    const uint32_t sb = (s & 4u) ? 0x7654u : 0x3210u;        // take the word one place up
-    const uint32_t sc = 0x3210u + 0x1111u * (s & 3u);        // funnel by 0..3 bytes
-    const uint32_t t0 = __byte_perm(o.x, o.z, sa), t1 = __byte_perm(o.y, o.w, sa), t2 = __byte_perm(o.z, n.x, sa),
-                   t3 = __byte_perm(o.w, n.y, sa), t4 = __byte_perm(n.x, n.z, sa), t5 = __byte_perm(n.y, n.w, sa);
-    const uint32_t u0 = __byte_perm(t0, t1, sb), u1 = __byte_perm(t1, t2, sb), u2 = __byte_perm(t2, t3, sb),
-                   u3 = __byte_perm(t3, t4, sb), u4 = __byte_perm(t4, t5, sb);
-    return make_uint4(__byte_perm(u0, u1, sc), __byte_perm(u1, u2, sc), __byte_perm(u2, u3, sc), __byte_perm(u3, u4, sc));
 }
 
 // q walks the UNALIGNED logical addresses A_j + 16 + 16 n; the load goes to the aligned vector below it
@@ -129,44 +105,6 @@ struct ColumnBatchesUA {
     }
 };
 
-// 16 accumulator words (byte r = row r) -> 4 rows x 4 words
-__device__ __forceinline__ void transpose_rows(const uint32_t *a, uint32_t (&r)[4][4], const uint32_t *t)
-{
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const uint32_t a0 = a[4 * q], a1 = a[4 * q + 1], a2 = a[4 * q + 2], a3 = a[4 * q + 3];
-        const uint32_t t0 = __byte_perm(a0, a1, 0x5140), t1 = __byte_perm(a2, a3, 0x5140);
-        const uint32_t t2 = __byte_perm(a0, a1, 0x7362), t3 = __byte_perm(a2, a3, 0x7362);
-        r[0][q] = __byte_perm(t0, t1, 0x5410);
-        r[1][q] = __byte_perm(t0, t1, 0x7632);
-        r[2][q] = __byte_perm(t2, t3, 0x5410);
-        r[3][q] = __byte_perm(t2, t3, 0x7632);
-        if (t) {
-            r[0][q] ^= t[q];
-            r[1][q] ^= t[4 + q];
-            r[2][q] ^= t[8 + q];
-            r[3][q] ^= t[12 + q];
-        }
-    }
-}
-
-// rows row0 .. row0+3 of window n: every lane hands its window to the lane below, which stores the aligned vector
-// that starts u bytes into its own window
-__device__ __forceinline__ void store_rows_ua(const uint32_t (&r)[4][4], const UaGeom &g, size_t n, int row0, int nrows, bool ok)
-{
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        if (i < nrows) {     // uniform
-            const uint4 own = make_uint4(r[i][0], r[i][1], r[i][2], r[i][3]);
-            const uint4 nx = shfl_next(own);
-            uint8_t *b = g.out_h + (ptrdiff_t)(row0 + i) * (ptrdiff_t)g.out_pitch + n * 16;
-            const uint32_t u = (0u - (uint32_t)reinterpret_cast<uintptr_t>(b)) & 15u;
-            const uint4 v = realign(own, nx, u);
-            if (ok) stg_stream(b + u, v);
-        }
-    }
-}
-
 template <int W, int K, int JB, int KB, int SP, bool PF, bool T7, bool PAD, bool XR>
 __device__ __forceinline__ void do_column_ua(uint4 (&buf0)[JB], uint4 (&buf1)[JB], const uint8_t *&q, const UaGeom &g, size_t n, size_t nn,
                                              bool have_next, bool have_next2, uint32_t lane, uint32_t lane_base, uint32_t tb,
@@ -182,19 +120,19 @@ __device__ __forceinline__ void do_column_ua(uint4 (&buf0)[JB], uint4 (&buf1)[JB
     uint32_t r[4][4];
     if constexpr (W == 8) {
         transpose_rows(acc.a, r, nullptr);
-        store_rows_ua(r, g, n, 0, g.nrows, ok);
+        store_rows_realigned(r, g.out_h, g.out_pitch, n, 0, g.nrows, ok);
         transpose_rows(acc.b, r, nullptr);
-        store_rows_ua(r, g, n, 4, g.nrows - 4, ok);
+        store_rows_realigned(r, g.out_h, g.out_pitch, n, 4, g.nrows - 4, ok);
     } else {
         transpose_rows(acc.a, r, (T7 && Map<K>::NF > Map<K>::N8) ? acc.t : nullptr);
-        store_rows_ua(r, g, n, 0, g.nrows, ok);
+        store_rows_realigned(r, g.out_h, g.out_pitch, n, 0, g.nrows, ok);
     }
     if constexpr (XR) {      // the peeled all-ones row: the row right above the group's rows
         r[0][0] = acc.x.x;
         r[0][1] = acc.x.y;
         r[0][2] = acc.x.z;
         r[0][3] = acc.x.w;
-        store_rows_ua(r, g, n, -1, 1, ok);
+        store_rows_realigned(r, g.out_h, g.out_pitch, n, -1, 1, ok);
     }
 }
 

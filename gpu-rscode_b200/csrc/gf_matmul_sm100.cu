@@ -22,6 +22,7 @@
 //   bank-conflicted shared tables, re-stages A and B into shared memory redundantly in every
 //   thread with two __syncthreads per tile, and moves 8 bytes per access.
 #include "gf_matmul_common.cuh"
+#include "gf_realign.cuh"
 #include "rs_internal.h"
 
 namespace rsgpu {
@@ -91,6 +92,85 @@ k_gf_matmul(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict
         if constexpr (W == 8) transpose_store(acc.b, out, out_pitch, v * 16, 4, nrows - 4);
         if constexpr (XR) stg_stream(out - out_pitch + v * 16, x);
         v = vn;
+    }
+}
+
+// Rows of any alignment on split-nibble tables (geometry and realignment: gf_realign.cuh) -- the counterpart of
+// gf_matmul_fat_ua_sm100.cu for every k that has no byte-table shape (25, 28, 33 .. 255), so that an odd pitch never
+// drops a long stripe onto the byte-per-thread kernel whatever the code.  Runtime loop over the fragments in batches of 4;
+// several blocks per SM hide the load latency (no software pipelining here: this is the fallback of a fallback).
+template <int W, bool XR>
+__global__ void __launch_bounds__(256)
+k_gf_matmul_ua(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
+               const uint32_t *__restrict__ tab, int npages, int k, int nrows, size_t nv, uint32_t hi4)
+{
+    extern __shared__ __align__(16) uint8_t s_raw[];
+    const uint32_t tb = ((uint32_t)__cvta_generic_to_shared(s_raw) + 255u) & ~255u;
+    {
+        constexpr int V4 = 32 * W / 16;
+        for (int i = threadIdx.x; i < npages * V4; i += blockDim.x) {
+            const int j = i / V4, r = i - j * V4;
+            const uint4 t = reinterpret_cast<const uint4 *>(tab)[i];
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(tb + j * 256 + r * 16), "r"(t.x), "r"(t.y),
+                         "r"(t.z), "r"(t.w) : "memory");
+        }
+    }
+    __syncthreads();
+
+    constexpr int JB = 4;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint8_t *in_h = in + kUaHead;
+    uint8_t *out_h = out + kUaHead;
+    const uint32_t s0 = (uint32_t)reinterpret_cast<uintptr_t>(in_h) & 15u, pm = (uint32_t)in_pitch & 15u;
+    const size_t nst = nv - 2, nspan = (nst + kUaSpan - 1) / kUaSpan;
+    const size_t wpb = blockDim.x >> 5, wtotal = (size_t)gridDim.x * wpb, nstride = wtotal * kUaSpan;
+    // loop control from blockIdx and kernel arguments only: whole warps at every shuffle
+    size_t S0 = (size_t)blockIdx.x * wpb;
+    size_t n = (S0 + (threadIdx.x >> 5)) * kUaSpan + lane;
+    for (; S0 < nspan; S0 += wtotal, n += nstride) {
+        Acc<W> acc;
+        acc_clear<W>(acc);
+        uint4 x = make_uint4(0u, 0u, 0u, 0u);
+        const bool inr = n < nv;
+        const uint8_t *q = in_h + n * 16;
+        uint32_t s = s0;
+        for (int j0 = 0; j0 < k; j0 += JB) {
+            uint4 d[JB];
+#pragma unroll
+            for (int jj = 0; jj < JB; ++jj) {
+                d[jj] = make_uint4(0u, 0u, 0u, 0u);
+                if (j0 + jj < k && inr)
+                    d[jj] = ldg_stream(reinterpret_cast<const uint8_t *>(reinterpret_cast<uintptr_t>(q) & ~(uintptr_t)15));
+                q += in_pitch;
+            }
+#pragma unroll
+            for (int jj = 0; jj < JB; ++jj) {
+                const uint4 w = realign(d[jj], shfl_next(d[jj]), s);     // padded slots: zeros against zero pages
+                s = (s + pm) & 15u;
+                mac_vec<W, 2>(w, tb + (uint32_t)(j0 + jj) * 256u, hi4, acc);
+                if constexpr (XR) {
+                    x.x ^= w.x;
+                    x.y ^= w.y;
+                    x.z ^= w.z;
+                    x.w ^= w.w;
+                }
+            }
+        }
+        const bool ok = lane < (uint32_t)kUaSpan && n < nst;
+        uint32_t r[4][4];
+        transpose_rows(acc.a, r, nullptr);
+        store_rows_realigned(r, out_h, out_pitch, n, 0, nrows, ok);
+        if constexpr (W == 8) {
+            transpose_rows(acc.b, r, nullptr);
+            store_rows_realigned(r, out_h, out_pitch, n, 4, nrows - 4, ok);
+        }
+        if constexpr (XR) {
+            r[0][0] = x.x;
+            r[0][1] = x.y;
+            r[0][2] = x.z;
+            r[0][3] = x.w;
+            store_rows_realigned(r, out_h, out_pitch, n, -1, 1, ok);
+        }
     }
 }
 
@@ -322,6 +402,23 @@ cudaError_t launch_matmul_group(const RowGroup &g, int k, int kpad,
             return launch_bytes(hi, len);
         }
         if (e != cudaErrorNotSupported) return e;
+        // no byte-table shape for this k: the same realignment on split-nibble tables
+        if (len >= (size_t)kUaHead + 48 + 16 * kUaSpan && (size_t)kpad * 256 + 256 <= (size_t)dev.max_smem_optin) {
+            using UaFn = void (*)(const uint8_t *, size_t, uint8_t *, size_t, const uint32_t *, int, int, int, size_t, uint32_t);
+            const UaFn fn = g.width == 4 ? (xr ? (UaFn)k_gf_matmul_ua<4, true> : (UaFn)k_gf_matmul_ua<4, false>) : (UaFn)k_gf_matmul_ua<8, false>;
+            const size_t smem = (size_t)kpad * 256 + 256;
+            int occ = 0;
+            if ((e = prepare_launch(dev, (const void *)fn, 256, smem, &occ)) != cudaSuccess) return e;
+            const size_t nv = (len - kUaHead) / 16, nst = nv - 2, nspan = (nst + kUaSpan - 1) / kUaSpan;
+            size_t want = (nspan + 7) / 8, cap = (size_t)dev.sm_count * occ;
+            if (tune.max_blocks > 0 && (size_t)tune.max_blocks < cap) cap = tune.max_blocks;
+            fn<<<(unsigned)(want < cap ? want : cap), 256, smem, s>>>(in, in_pitch, out_g, out_pitch, g.d_tab, kpad, k, g.nrows, nv,
+                                                                    16u * g.width * 0x01010101u);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            if (launches) ++*launches;
+            if ((e = launch_bytes(0, kUaHead + 16)) != cudaSuccess) return e;
+            return launch_bytes((size_t)kUaHead + 16 * nst, len);
+        }
     }
 
     // a single all-ones row: XOR of the inputs, no lookups (the byte tail below still uses the tables, which exist)

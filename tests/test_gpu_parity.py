@@ -308,6 +308,13 @@ UNALIGNED_CASES = [
     (12, 9, (1 << 20) + 3, 0, 0, 9, 3),            # two row groups (8 + 1)
     (9, 4, (1 << 20) + 3, 0, 0, 6, 10),            # odd batch count (3 x 3)
     (5, 3, 1_048_576 + 480 * 7 + 1, 0, 0, 13, 14),
+    # k without a byte-table shape: the same realignment on split-nibble tables
+    (25, 4, (1 << 20) + 3, 0, 0, 1, 2),
+    (28, 3, (1 << 20) + 9, 0, 0, 0, 0),
+    (40, 5, (1 << 20) + 1, 0, 0, 5, 5),            # peeled XOR row
+    (64, 8, (1 << 20) + 5, 0, 0, 3, 7),            # 64-bit entries
+    (100, 2, (1 << 20) + 7, 2, 6, 9, 9),
+    (255, 1, (1 << 20) + 11, 0, 0, 15, 0),
 ]
 
 

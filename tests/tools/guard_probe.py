@@ -81,6 +81,8 @@ CASES = [
     (27, 4, 16 * 65_539, 0, 6),                 # register-fed nibble kernel, padded batches
     (64, 4, 16 * 1536 * 3 + 16 * 77 + 9, 7, 9),  # multi-pass kernel + remainder + tail
     (40, 5, 16 * 1536 * 2, 0, 9),
+    (28, 4, (1 << 20) + 3, 0, 0), (64, 8, (1 << 20) + 5, 0, 0), (33, 5, (1 << 20) + 9, 0, 0),   # realigning nibble kernel
+    (10, 1, (1 << 20) + 16 * 3, 0, 0), (40, 1, (2 << 20) + 5, 11, 0),    # XOR kernel + tail
     (10, 4, 1000, 0, 0), (10, 4, 15, 0, 0),     # byte kernel only
 ]
 
