@@ -357,9 +357,12 @@ __device__ __forceinline__ void build_block_tables(uint32_t tb, const uint32_t *
 
 // which instances use the L2 prefetch / the transposed bit-7 accumulation (measurements: make_fat)
 __host__ __device__ constexpr bool fat_use_prefetch(int K) { return K >= 8; }
+#ifndef RSGPU_T7_K10
+#define RSGPU_T7_K10 0     // experiment switch: transposed bit-7 terms for the k = 10 shape too (sustained rate)
+#endif
 __host__ __device__ constexpr bool fat_use_t7(int W, int K)
 {
-    return W == 4 && (K == 12 || K == 14 || K == 16 || K == 18 || K == 20);
+    return W == 4 && (K == 12 || K == 14 || K == 16 || K == 18 || K == 20 || (RSGPU_T7_K10 && K == 10));
 }
 
 }  // namespace
