@@ -11,9 +11,10 @@
 //     16-byte windows; window n of row j straddles the aligned vectors n and n+1 of that row's own aligned
 //     grid, at the row's byte offset s_j = (A_j + 16) & 15 (the same for every window of the row).
 //   * lane l of a warp loads aligned vector 30 S + l of every row (S = span index of the warp); the vector
-//     n+1 comes from lane l+1 by four SHFL.DOWN; a branch-free funnel (two select stages for the word
-//     offset, one PRMT stage for the byte offset; s_j is warp-uniform) yields the window.  Lanes 0..30 of a
-//     span hold valid windows; the multiply-accumulate is the byte-table code of gf_matmul_fat.cuh, unchanged.
+//     n+1 comes from lane l+1 by four SHFL.DOWN; a branch-free funnel of three PRMT stages (shift by 8, by 4,
+//     by 0..3 bytes; s_j is the same for the whole grid, so the selectors live in uniform registers; gf_realign.cuh)
+//     yields the window.  Lanes 0..30 of a span hold valid windows; the multiply-accumulate is the byte-table
+//     code of gf_matmul_fat.cuh, unchanged.
 //   * the outputs are realigned the same way: output row i has its offset u_i to the next 16-byte boundary; the
 //     aligned vector that starts there takes bytes [u_i, 16) of window n and [0, u_i) of window n+1 -- lane l+1
 //     again -- so lanes 0..29 store one ALIGNED 128-bit vector per row.  Spans advance by 30 windows: 2 of 32
@@ -21,6 +22,8 @@
 //     byte loops and no divergence anywhere in the steady state; sector traffic to L2 is that of aligned rows.
 //   * the first 32 and the last < 48 bytes of every row (where an aligned vector would reach outside the row)
 //     go to the byte kernel, as before.
+// Measured: RS(10,14), L = 400 MiB + 3, pitch = L: 0.750 of the HBM peak (byte kernel 0.207, aligned rows 1.0); alu pipe
+// 84 %, issue 73 % (profiles/r2_ncu_full_ua_rs1014.csv).  k without a byte-table shape: k_gf_matmul_ua (gf_matmul_sm100.cu).
 #include "gf_matmul_fat.cuh"
 #include "gf_realign.cuh"
 

@@ -91,6 +91,11 @@ int rsgpu_get_total_matrix(rsgpu_ctx *ctx, uint8_t *total_matrix);
  * Replaces encode_chunk (src/matrix.h:80, src/matrix.cu:767-830) and both matrix_mul kernels
  * (src/matrix.cu:232-323, 335-407).  Unlike the reference it overwrites parity (no pre-zeroing
  * needed), takes pitches, 64-bit len, and never synchronises.
+ * Alignment: bases and pitches that are multiples of 16 bytes run at the HBM roofline.  Any other alignment -- e.g.
+ * pitch = ceil(size / k), a file's fragments held back to back -- is coded by a kernel that reads and writes aligned
+ * 128-bit vectors and realigns them in registers (about 0.75 of the roofline from 1 MiB per fragment on; the reference
+ * drops to a byte-per-thread kernel whenever the length is not a multiple of 8, src/matrix.cu:796,811).  Same bytes.
+ * A code with ONE parity row (p = 1: all coefficients 1) is a plain XOR of the fragments and runs without tables.
  * Byte columns are independent, so a BATCH of stripes stored fragment-major -- row j = fragment j of
  * stripe 0, then of stripe 1, ... (pitch = stripes * stripe_len) -- is one call with len = stripes *
  * stripe_len: one launch, tables built once, which is how small stripes reach the large-stripe rate.
@@ -161,7 +166,8 @@ int rsgpu_decode(rsgpu_ctx *ctx, const uint8_t *survivors_d, size_t survivors_pi
 /*
  * Decode only what was lost: out row t is native rsgpu_get_erased().idx[t].  Same inputs as
  * rsgpu_decode; writes e*len instead of k*len bytes (the reference always rewrites all k,
- * src/matrix.cu:881).
+ * src/matrix.cu:881).  One lost native whose survivors are the other natives plus parity row 0 -- the
+ * commonest repair -- is recognised as a plain XOR of the survivors (no lookups, HBM speed for any k).
  */
 int rsgpu_decode_erased(rsgpu_ctx *ctx, const uint8_t *survivors_d, size_t survivors_pitch,
                         uint8_t *out_d, size_t out_pitch, size_t len, void *stream);
