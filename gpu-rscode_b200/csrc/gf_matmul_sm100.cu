@@ -97,8 +97,8 @@ k_gf_matmul(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict
 
 // Rows of any alignment on split-nibble tables (geometry and realignment: gf_realign.cuh) -- the counterpart of
 // gf_matmul_fat_ua_sm100.cu for every k that has no byte-table shape (25, 28, 33 .. 255), so that an odd pitch never
-// drops a long stripe onto the byte-per-thread kernel whatever the code.  Runtime loop over the fragments in batches of 4;
-// several blocks per SM hide the load latency (no software pipelining here: this is the fallback of a fallback).
+// drops a long stripe onto the byte-per-thread kernel whatever the code.  Runtime loop over the fragments in batches of 4,
+// the next batch loaded while the current one is consumed; several blocks per SM.
 template <int W, bool XR>
 __global__ void __launch_bounds__(256)
 k_gf_matmul_ua(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restrict__ out, size_t out_pitch,
@@ -134,8 +134,9 @@ k_gf_matmul_ua(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restr
         const bool inr = n < nv;
         const uint8_t *q = in_h + n * 16;
         uint32_t s = s0;
-        for (int j0 = 0; j0 < k; j0 += JB) {
-            uint4 d[JB];
+        // the next batch of four rows is in flight while the current one is consumed (ncu of the first version, which
+        // loaded and used batch by batch: long-scoreboard 6.5 stalls per issued instruction)
+        auto load4 = [&](uint4 (&d)[JB], int j0) {
 #pragma unroll
             for (int jj = 0; jj < JB; ++jj) {
                 d[jj] = make_uint4(0u, 0u, 0u, 0u);
@@ -143,6 +144,14 @@ k_gf_matmul_ua(const uint8_t *__restrict__ in, size_t in_pitch, uint8_t *__restr
                     d[jj] = ldg_stream(reinterpret_cast<const uint8_t *>(reinterpret_cast<uintptr_t>(q) & ~(uintptr_t)15));
                 q += in_pitch;
             }
+        };
+        uint4 nxt[JB];
+        load4(nxt, 0);
+        for (int j0 = 0; j0 < k; j0 += JB) {
+            uint4 d[JB];
+#pragma unroll
+            for (int jj = 0; jj < JB; ++jj) d[jj] = nxt[jj];
+            if (j0 + JB < k) load4(nxt, j0 + JB);
 #pragma unroll
             for (int jj = 0; jj < JB; ++jj) {
                 const uint4 w = realign(d[jj], shfl_next(d[jj]), s);     // padded slots: zeros against zero pages
