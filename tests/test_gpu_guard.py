@@ -17,6 +17,8 @@ def test_no_kernel_touches_memory_outside_its_buffers():
     if not torch.cuda.is_available():
         pytest.skip("needs a CUDA device")
     r = subprocess.run([sys.executable, os.path.join(HERE, "tools", "guard_probe.py")], capture_output=True, text=True, timeout=900)
+    if r.returncode == 77:
+        pytest.skip("cuda-python (cuda.bindings) is not importable here")
     assert r.returncode == 0 and "guard ok:" in r.stdout, (r.stdout[-1500:] + "\n" + r.stderr[-3000:])
 
 
@@ -27,4 +29,6 @@ def test_the_guard_catches_an_overrun():
         pytest.skip("needs a CUDA device")
     r = subprocess.run([sys.executable, os.path.join(HERE, "tools", "guard_probe.py"), "--selftest"], capture_output=True, text=True,
                        timeout=300)
-    assert r.returncode != 0 and "UNNOTICED" not in r.stdout, r.stdout[-1000:] + r.stderr[-1000:]
+    if r.returncode == 77:
+        pytest.skip("cuda-python (cuda.bindings) is not importable here")
+    assert r.returncode == 3 and "UNNOTICED" not in r.stdout, r.stdout[-1000:] + r.stderr[-1000:]
