@@ -845,6 +845,37 @@ def test_fuzz_encode_shapes_vs_oracle(rs, orc, torch):
     run()
 
 
+def test_fuzz_unaligned_long_rows_vs_byte_kernel(rs, orc, torch):
+    """Random codes, lengths just above the realigning kernels' threshold, random base offsets and pitch slack on both
+    sides: the realigning kernels (byte tables or split-nibble tables, whichever the code gets) must write exactly what
+    the byte kernel alone (variant 6) writes -- guard bytes included -- and a window of it is checked against the oracle."""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=25, deadline=None, derandomize=True, suppress_health_check=list(HealthCheck))
+    @given(k=st.integers(2, 48), p=st.sampled_from([1, 2, 3, 4, 5, 8, 9]), extra=st.integers(0, 5000), dpi=st.integers(0, 33),
+           dpo=st.integers(0, 33), in_off=st.integers(0, 31), out_off=st.integers(0, 31), seed=st.integers(0, 2**31))
+    def run(k, p, extra, dpi, dpo, in_off, out_off, seed):
+        L = (1 << 20) + extra
+        pi, po = L + dpi, L + dpo
+        g = torch.Generator(device="cuda").manual_seed(seed)
+        buf = torch.randint(0, 256, (k * pi + in_off + 64,), dtype=torch.uint8, device="cuda", generator=g)
+        out = torch.full((p * po + out_off + 64,), 0xEE, dtype=torch.uint8, device="cuda")
+        out6 = torch.full_like(out, 0xEE)
+        stream = torch.cuda.current_stream().cuda_stream
+        with rs.RSContext(k, p) as ctx:
+            ctx.encode(buf.data_ptr() + in_off, pi, out.data_ptr() + out_off, po, L, stream)
+            ctx.set_tuning(variant=6)
+            ctx.encode(buf.data_ptr() + in_off, pi, out6.data_ptr() + out_off, po, L, stream)
+            torch.cuda.synchronize()
+        assert torch.equal(out, out6), (k, p, L, dpi, dpo, in_off, out_off)
+        c0 = (seed % (L - 3000))
+        data = buf[in_off:in_off + k * pi].view(k, pi)[:, c0:c0 + 3000].cpu().numpy()
+        got = out[out_off:out_off + p * po].view(p, po)[:, c0:c0 + 3000].cpu().numpy()
+        assert (got == orc.matrix_mul(orc.gen_encoding_matrix(p, k), data)).all(), (k, p, L, c0)
+
+    run()
+
+
 def test_fuzz_encode_batch_vs_per_stripe_calls(rs, orc, torch):
     """Random batch geometries: the one-call result must equal rsgpu_encode stripe by stripe (itself checked
     against the oracle above), and stripe 0 is checked against the oracle directly."""
